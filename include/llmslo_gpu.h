@@ -1,0 +1,279 @@
+/*
+ * llmslo_gpu.h — C ABI of libllmslo_gpu.so: the B200 (sm_100a) batch correlation + attribution path
+ * of llm-slo-ebpf-toolkit.
+ *
+ * The reference (Go, CGO_ENABLED=0) has no FFI seam; the drop-in boundary is a set of exported Go
+ * functions.  Each entry point below names the Go function(s) whose arithmetic it
+ * replaces, as file:line under the reference tree.  The cgo binding a maintainer would add
+ * (pkg/gpu) is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - plain pointers and sizes; no C++ types, no exceptions, no abort().  Return 0 on success, a
+ *     negative LSG_ERR_* otherwise; lsg_last_error(ctx) gives the text until the next call on ctx.
+ *   - the caller owns every buffer.  Functions without a suffix take HOST pointers and copy in/out
+ *     on the context's stream (pinned host memory makes those copies asynchronous); `_dev`
+ *     functions take DEVICE pointers on the context's device and leave results on the device.
+ *     Every call returns after its work on the context's stream has completed, except `_dev`
+ *     calls documented as asynchronous.
+ *   - a context is bound to one device and one stream and is NOT thread-safe.
+ *   - there is no CPU fallback: without a usable CUDA device lsg_create fails.
+ *
+ * Interned identities.  Strings are dictionary-encoded by the caller (0 = empty string).  A record
+ * does not carry pod/node/service directly but an `ident`: a row of the identity table holding the
+ * interned (pod, node, service) triple seen on that record, plus `grp`, the join group.
+ *
+ *   JOIN-GROUP CONTRACT (checked by nobody but the interner): any span/event pair for which the
+ *   reference Match() (pkg/correlation/dns.go:50-76) can return Matched must have the same
+ *   non-zero grp.  The interner gets this by union-find over identity rows: rows sharing a
+ *   non-empty pod, rows sharing a non-empty (service, node), and rows that carry the same
+ *   non-empty trace id are merged.  grp 0 means "matches nothing".  Within a group the library
+ *   evaluates the complete four-tier Match() on every pair inside the outer window, so coarser
+ *   groups are always correct, only slower.
+ */
+#ifndef LLMSLO_GPU_H
+#define LLMSLO_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LSG_NSIG 12            /* supported signals, in DefaultLikelihoods order (bayesian.go:69-189)      */
+#define LSG_NDOM 8             /* fault domains, AllDomains() order (bayesian.go:23-34)                    */
+#define LSG_SIG_UNSUPPORTED 15 /* signalAttrKey() default branch (ebpfcorrelator/correlator.go:143-172)    */
+#define LSG_TRACE_BITS 28      /* events pack trace id and signal into one word                            */
+#define LSG_TS_ZERO INT64_MIN  /* time.Time{}.IsZero() (dns.go:108); Unix 0 is a valid time                */
+#define LSG_NONE 0xFFFFFFFFu   /* "no event" / "no incident"                                               */
+#define LSG_MAX_FANOUT 8
+#define LSG_MAX_ACTUAL 16      /* rows of the confusion matrix: 8 domains + up to 8 other actual strings   */
+#define LSG_MAX_WINDOW_NS (((int64_t)1 << 53) - 1) /* float64(Duration) compare in dns.go:111-112 is exact below this */
+
+/* tiers of Match(), dns.go:58-73.  confidence = {0, 1.0, 0.9, 0.8, 0.65}[tier] */
+enum { LSG_TIER_NONE = 0, LSG_TIER_TRACE = 1, LSG_TIER_POD_PID = 2, LSG_TIER_POD_CONN = 3, LSG_TIER_SVC_NODE = 4 };
+
+enum {
+  LSG_OK = 0,
+  LSG_ERR_INVALID = -1,   /* bad argument (null pointer, fanout out of range, window too large, ...)  */
+  LSG_ERR_CUDA = -2,      /* a CUDA runtime call failed; text in lsg_last_error                      */
+  LSG_ERR_NOMEM = -3,     /* device or host allocation failed                                        */
+  LSG_ERR_RANGE = -4,     /* an id in a record is outside its table (ident, trace >= 2^28, class ...) */
+  LSG_ERR_NODEVICE = -5   /* no CUDA device: there is no CPU path                                     */
+};
+
+/* SignalRef (dns.go:30-40) after interning: 32 bytes. */
+typedef struct {
+  int64_t ts_ns;      /* Unix ns; LSG_TS_ZERO for the zero Time                                    */
+  double value;       /* SignalRef.Value                                                          */
+  uint32_t ident;     /* row of the identity table                                                */
+  uint32_t pid;       /* PID if > 0 else 0                                                        */
+  uint32_t conn;      /* interned ConnTuple                                                       */
+  uint32_t trace_sig; /* (interned TraceID << 4) | signal index (0..11, or LSG_SIG_UNSUPPORTED)   */
+} lsg_event;
+
+/* SpanRef (dns.go:19-27) / SpanRecord (processor.go:10-20) after interning: 32 bytes. */
+typedef struct {
+  int64_t ts_ns;
+  uint32_t ident;
+  uint32_t pid;
+  uint32_t conn;
+  uint32_t trace;     /* interned TraceID, < 2^28                                                  */
+  uint32_t incident;  /* incident this span belongs to (A7 glue), or LSG_NONE                      */
+  uint32_t reserved;  /* must be 0                                                                 */
+} lsg_span;
+
+/* identity table row */
+typedef struct {
+  uint32_t pod, node, service; /* interned strings, 0 = empty                                      */
+  uint32_t grp;                /* join group, see contract above; 0 = matches nothing              */
+} lsg_ident;
+
+/* DebugStats (correlator.go:20-25), summed over spans as mergeDebug does (processor.go:51-58). */
+typedef struct {
+  uint64_t unmatched, low_confidence, fanout_dropped, unsupported_type;
+} lsg_debug;
+
+/* integer part of EvalReport (evaluator.go:34-51); ratios are formed by the caller. */
+typedef struct {
+  uint64_t tp, fp, fn, tn;
+  uint64_t tier_correct, tier_comparable;
+  uint64_t predicted_by_tier[5]; /* predicted pairs per tier; mean confidence = sum(n[t]*conf[t]) / sum(n[t]) */
+  uint64_t matched_by_tier[5];   /* all pairs per Match() tier, [0] = unmatched                              */
+} lsg_eval;
+
+/* BayesianAttributor (bayesian.go:39-42) flattened.  NaN in lik = domain missing from that signal's
+ * map (likelihoodFor returns 0.5, bayesian.go:293-296); NaN in thresh = no threshold. */
+typedef struct {
+  double prior[LSG_NDOM];          /* b.Priors in AllDomains order; <= 0 becomes 1e-10 (bayesian.go:231-233) */
+  double lik[LSG_NSIG][LSG_NDOM];  /* b.Likelihoods[signal][domain]                                          */
+  double thresh[LSG_NSIG];         /* signalThresholds (bayesian.go:193-206)                                 */
+  double log_extra[LSG_NDOM];      /* sum of log clamp(1-p) over Likelihoods entries outside the 12 signals  */
+  uint32_t sig_mask;               /* bit s set = signal s is a key of b.Likelihoods                         */
+  uint32_t reserved;
+} lsg_model;
+
+/* integer part of Accuracy / PartialAccuracy / CoverageAccuracy and BuildConfusionMatrix (pipeline.go:65-185) */
+typedef struct {
+  uint64_t matrix[LSG_MAX_ACTUAL][LSG_NDOM]; /* [actual class][predicted domain]                   */
+  uint64_t n;                                /* incidents counted                                  */
+  uint64_t correct;                          /* Accuracy numerator                                 */
+  uint64_t partial;                          /* PartialAccuracy numerator                          */
+  uint64_t coverage[LSG_NDOM + 1][LSG_NDOM + 1]; /* [found][len(expected)] histogram; coverage accuracy = sum h*found/len / n */
+} lsg_confusion_out;
+
+/* per (incident, signal) features of the A7 glue.  Only `max` has a reference counterpart
+ * (correlator.go:109-111); count/sum/sketch are defined by this library (oracle/oracle.h). */
+#define LSG_SKETCH_BINS 16
+typedef struct {
+  uint32_t count;                    /* spans of the incident that carry the signal        */
+  uint32_t sketch[LSG_SKETCH_BINS];  /* log2 histogram of the per-span values              */
+  double sum;                        /* sum of the per-span values (span order)            */
+} lsg_feature;
+
+typedef struct lsg_ctx lsg_ctx;
+
+/* ---- context ------------------------------------------------------------------------------ */
+/* device: CUDA ordinal.  stream: a cudaStream_t (as void*) to run on, or NULL for a private one. */
+int lsg_create(int device, void *stream, lsg_ctx **out);
+void lsg_destroy(lsg_ctx *ctx);
+const char *lsg_last_error(const lsg_ctx *ctx);
+const char *lsg_version(void);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+uint64_t lsg_launch_count(const lsg_ctx *ctx);
+/* bytes of device workspace currently held */
+size_t lsg_workspace_bytes(const lsg_ctx *ctx);
+
+/* NewBayesianAttributor() defaults (bayesian.go:46-207) */
+void lsg_default_model(lsg_model *out);
+/* replaces reading b.Priors / b.Likelihoods inside Attribute (bayesian.go:230-242) */
+int lsg_set_model(lsg_ctx *ctx, const lsg_model *model);
+
+/* ---- A2-A3: correlation.Match (dns.go:50-76) over pre-paired records, and
+ *      correlation.EvaluateLabeledPairs (evaluator.go:90-167) ------------------------------- */
+int lsg_match_pairs(lsg_ctx *ctx, const lsg_span *spans, const lsg_event *events, size_t n,
+                    const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold,
+                    const uint8_t *expected_match /* n or NULL */, const uint8_t *expected_tier /* n or NULL; 0 = none */,
+                    uint8_t *tier_out /* n */, uint8_t *predicted_out /* n */, lsg_eval *eval_out);
+int lsg_match_pairs_dev(lsg_ctx *ctx, const lsg_span *spans, const lsg_event *events, size_t n,
+                        const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold,
+                        const uint8_t *expected_match, const uint8_t *expected_tier,
+                        uint8_t *tier_out, uint8_t *predicted_out, lsg_eval *eval_out /* HOST */);
+
+/* ---- A4-A6: Correlator.ProcessBatch (ebpfcorrelator/processor.go:29-49) =
+ *      EnrichAttributes (correlator.go:50-125) per span + DecomposeRetrieval (correlator.go:179-194)
+ *
+ *  window_ns <= 0 -> 2 s; threshold <= 0 -> 0.7; fanout <= 0 -> 3 (dns.go:51-53, correlator.go:58-66).
+ *  cand_event  [n_spans*fanout] index into `events` of the kept candidates in reference order
+ *              (confidence desc, |dt| asc, input order), LSG_NONE = none
+ *  cand_tier   [n_spans*fanout] tier of each kept candidate, 0 = none
+ *  attr_base   [n_spans*12] or NULL: SpanRecord.Attributes on entry, NaN = absent
+ *  attr_out    [n_spans*12] enriched attributes, NaN = absent (correlator.go:106-112)
+ *  conf_out    [n_spans] llm.ebpf.correlation_confidence, 0 = not set (correlator.go:113-118)
+ *  retrieval_out [n_spans] or NULL: DecomposeRetrieval total (attribute is set when > 0)
+ *  n_cand_out  [n_spans] or NULL: candidates >= threshold before the fanout cut
+ *  Any output pointer except cand_event/cand_tier/attr_out/conf_out may be NULL. */
+int lsg_process_batch(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                      const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
+                      const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out,
+                      double *conf_out, double *retrieval_out, uint32_t *n_cand_out, lsg_debug *debug_out);
+int lsg_process_batch_dev(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                          const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
+                          const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out,
+                          double *conf_out, double *retrieval_out, uint32_t *n_cand_out, lsg_debug *debug_out /* HOST */);
+
+/* the sort stage alone (device pointers): stable sort of events by (grp, ts); writes the sorted
+ * records and, if not NULL, the permutation (sorted position -> input index) and the sort keys. */
+int lsg_sort_events_dev(lsg_ctx *ctx, const lsg_event *events, size_t n_events, const lsg_ident *idents, size_t n_idents,
+                        lsg_event *sorted_out, uint32_t *perm_out, uint64_t *keys_out);
+
+/* ---- A7 glue: per incident, per signal max over its spans' enriched attributes
+ *      (aggregate = max as in correlator.go:109-111; FaultSample.Signals, mapper.go:20).
+ *  span_incident [n_spans] incident index or LSG_NONE;  signals_out [n_incidents*12], NaN = absent;
+ *  features_out [n_incidents*12] or NULL. */
+int lsg_incident_features(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
+                          size_t n_incidents, double *signals_out, lsg_feature *features_out);
+int lsg_incident_features_dev(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
+                              size_t n_incidents, double *signals_out, lsg_feature *features_out);
+
+/* ---- A9-A10: BayesianAttributor.Attribute (bayesian.go:218-284) and the numeric part of
+ *      AttributeSample (bayesian.go:315-343) for a batch of incidents.
+ *  signals     [n*12] FaultSample.Signals by signal index, NaN = key absent
+ *  has_signals [n] or NULL: len(sample.Signals) > 0 (NULL = derive: any non-NaN)
+ *  rule_label  [n] or NULL: MapFaultLabel(sample.FaultLabel) as a domain index, used when !has_signals
+ *  posterior   [n*8] AllDomains order (all NaN when !has_signals)
+ *  top1        [n] predicted domain: first maximum of the posteriors in AllDomains order
+ *              (sort.SliceStable, bayesian.go:279-281), or rule_label (0xFF if NULL) when !has_signals
+ *  elev_mask   [n] or NULL: bit s = signal s elevated (bayesian.go:220-225) */
+int lsg_attribute(lsg_ctx *ctx, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
+                  double *posterior, uint8_t *top1, uint16_t *elev_mask);
+int lsg_attribute_dev(lsg_ctx *ctx, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
+                      double *posterior, uint8_t *top1, uint16_t *elev_mask);
+
+/* ---- A12-A13: BuildConfusionMatrix, Accuracy, PartialAccuracy, CoverageAccuracy (pipeline.go:65-185)
+ *  actual      [n] class of ExpectedDomain or MapFaultLabel(FaultLabel): 0..7 = AllDomains, 8..15 = other strings
+ *  predicted   [n] PredictedFaultDomain, 0..7
+ *  expected    [n] ExpectedDomains as nibbles (first element in the low nibble; 0..7 domain, 0xF other), or
+ *              the one-element fallback list of pipeline.go:119-126
+ *  expected_n  [n] length of that list, 1..8
+ *  posterior   [n*8] or NULL (no hypotheses, the rule path); entries NaN = no hypothesis
+ *  coverage_thr threshold of CoverageAccuracy (pipeline.go:163-167)
+ *  hyp_floor   entries below it are not hypotheses: 0.01 when `posterior` is the raw output of lsg_attribute
+ *              (AttributeSample's filter, bayesian.go:326-328), 0 when it already is a hypothesis list */
+int lsg_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted, const uint32_t *expected,
+                  const uint8_t *expected_n, const double *posterior, double coverage_thr, double hyp_floor,
+                  size_t n, lsg_confusion_out *out);
+int lsg_confusion_dev(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted, const uint32_t *expected,
+                      const uint8_t *expected_n, const double *posterior, double coverage_thr, double hyp_floor,
+                      size_t n, lsg_confusion_out *out /* HOST */);
+
+/* ---- the whole hot path on device-resident input (bench.py's timed step):
+ *      sort -> join -> per-span features -> per-incident features -> attribution -> confusion.
+ *  `counters_dev` (device, LSG_COUNTER_WORDS u64) receives every integer result in one block so
+ *  that a multi-GPU caller can sum-allreduce it; layout = lsg_counters. */
+typedef struct {
+  lsg_debug debug;
+  lsg_confusion_out confusion;
+  uint64_t events, spans, incidents, candidates, kept;
+} lsg_counters;
+#define LSG_COUNTER_WORDS (sizeof(lsg_counters) / 8)
+
+typedef struct {
+  const lsg_span *spans; size_t n_spans;
+  const lsg_event *events; size_t n_events;
+  const lsg_ident *idents; size_t n_idents;
+  size_t n_incidents;
+  const uint8_t *inc_actual;     /* [n_incidents] */
+  const uint32_t *inc_expected;  /* [n_incidents] */
+  const uint8_t *inc_expected_n; /* [n_incidents] */
+  int64_t window_ns; double threshold; int fanout; double coverage_thr;
+  /* outputs (device) */
+  uint32_t *cand_event; uint8_t *cand_tier; double *attr_out; double *conf_out;
+  double *inc_signals; double *posterior; uint8_t *top1;
+  uint64_t *counters_dev;
+} lsg_pipeline_args;
+/* asynchronous: returns after enqueueing on the context's stream */
+int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *args);
+
+/* ---- synthetic workload: record i is a pure function of (seed, i), generated on
+ *      the device by lsg_synth_dev and on the host by lsg_synth_host with identical results. */
+typedef struct {
+  uint64_t seed;
+  uint64_t n_events, n_spans;
+  uint32_t n_pods, pods_per_node, pods_per_group;
+  uint32_t spans_per_incident;
+  uint32_t multi_fault;        /* 0: single-fault incidents; 1: 2-3 concurrent faults               */
+  int64_t t0_ns, horizon_ns;
+  uint32_t rank, world;        /* shard: this rank's pods are [rank*n_pods, (rank+1)*n_pods) of the global space */
+} lsg_synth_cfg;
+size_t lsg_synth_n_idents(const lsg_synth_cfg *cfg);
+size_t lsg_synth_n_incidents(const lsg_synth_cfg *cfg);
+int lsg_synth_dev(lsg_ctx *ctx, const lsg_synth_cfg *cfg, lsg_span *spans, lsg_event *events, lsg_ident *idents,
+                  uint8_t *inc_actual, uint32_t *inc_expected, uint8_t *inc_expected_n);
+int lsg_synth_host(const lsg_synth_cfg *cfg, lsg_span *spans, lsg_event *events, lsg_ident *idents,
+                   uint8_t *inc_actual, uint32_t *inc_expected, uint8_t *inc_expected_n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMSLO_GPU_H */

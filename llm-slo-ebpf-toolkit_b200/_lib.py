@@ -1,0 +1,211 @@
+"""ctypes loader and thin typed wrapper over the C ABI (include/llmslo_gpu.h).
+
+The product path fails loudly: a missing library raises LsgError at first use, a missing CUDA
+device makes lsg_create return LSG_ERR_NODEVICE.  Nothing here computes on the CPU.
+"""
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+from . import _abi as A
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+_LOCK = threading.Lock()
+
+
+class LsgError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libllmslo_gpu: %s (code %d)" % (msg, code))
+        self.code = code
+
+
+def lib_path():
+    return os.environ.get("LLMSLO_GPU_LIB", os.path.join(_HERE, "libllmslo_gpu.so"))
+
+
+def load_library():
+    """dlopen libllmslo_gpu.so (built in-tree by __graft_entry__.build()) and declare prototypes."""
+    global _LIB
+    with _LOCK:
+        if _LIB is not None:
+            return _LIB
+        path = lib_path()
+        if not os.path.exists(path):
+            raise LsgError(-5, "%s not found: run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                               "there is no CPU fallback" % path)
+        lib = C.CDLL(path)
+        vp, sz, i64, dbl, cint = C.c_void_p, C.c_size_t, C.c_int64, C.c_double, C.c_int
+        P = C.POINTER
+        lib.lsg_create.argtypes = [cint, vp, P(vp)]
+        lib.lsg_destroy.argtypes = [vp]
+        lib.lsg_destroy.restype = None
+        lib.lsg_last_error.argtypes = [vp]
+        lib.lsg_last_error.restype = C.c_char_p
+        lib.lsg_version.restype = C.c_char_p
+        lib.lsg_launch_count.argtypes = [vp]
+        lib.lsg_launch_count.restype = C.c_uint64
+        lib.lsg_workspace_bytes.argtypes = [vp]
+        lib.lsg_workspace_bytes.restype = sz
+        lib.lsg_default_model.argtypes = [P(A.Model)]
+        lib.lsg_default_model.restype = None
+        lib.lsg_set_model.argtypes = [vp, P(A.Model)]
+        for name in ("lsg_match_pairs", "lsg_match_pairs_dev"):
+            getattr(lib, name).argtypes = [vp, vp, vp, sz, vp, sz, i64, dbl, vp, vp, vp, vp, P(A.Eval)]
+        for name in ("lsg_process_batch", "lsg_process_batch_dev"):
+            getattr(lib, name).argtypes = [vp, vp, sz, vp, sz, vp, sz, i64, dbl, cint, vp, vp, vp, vp, vp, vp, vp,
+                                           P(A.Debug)]
+        lib.lsg_sort_events_dev.argtypes = [vp, vp, sz, vp, sz, vp, vp, vp]
+        for name in ("lsg_incident_features", "lsg_incident_features_dev"):
+            getattr(lib, name).argtypes = [vp, vp, vp, sz, sz, vp, vp]
+        for name in ("lsg_attribute", "lsg_attribute_dev"):
+            getattr(lib, name).argtypes = [vp, vp, vp, vp, sz, vp, vp, vp]
+        for name in ("lsg_confusion", "lsg_confusion_dev"):
+            getattr(lib, name).argtypes = [vp, vp, vp, vp, vp, vp, dbl, dbl, sz, P(A.ConfusionOut)]
+        lib.lsg_pipeline_dev.argtypes = [vp, P(A.PipelineArgs)]
+        lib.lsg_synth_n_idents.argtypes = [P(A.SynthCfg)]
+        lib.lsg_synth_n_idents.restype = sz
+        lib.lsg_synth_n_incidents.argtypes = [P(A.SynthCfg)]
+        lib.lsg_synth_n_incidents.restype = sz
+        lib.lsg_synth_dev.argtypes = [vp, P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
+        lib.lsg_synth_host.argtypes = [P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
+        lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
+        lib.lsg_abi_sizes.restype = cint
+        _LIB = lib
+        return lib
+
+
+def _ptr(a):
+    """host numpy array (or None) -> void*"""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"], "array must be C-contiguous"
+    return a.ctypes.data
+
+
+def _as(a, dtype):
+    if a is None:
+        return None
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+class Context:
+    """One lsg_ctx: one device, one stream.  Not thread-safe (as the C ABI says)."""
+
+    def __init__(self, device=0, stream=None):
+        self._lib = load_library()
+        h = C.c_void_p()
+        rc = self._lib.lsg_create(int(device), C.c_void_p(stream) if stream else None, C.byref(h))
+        if rc != 0:
+            raise LsgError(rc, "lsg_create failed: no usable CUDA device %d (there is no CPU path)" % device)
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.lsg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise LsgError(rc, (self._lib.lsg_last_error(self._h) or b"?").decode())
+
+    @property
+    def handle(self):
+        return self._h
+
+    def launch_count(self):
+        return int(self._lib.lsg_launch_count(self._h))
+
+    def workspace_bytes(self):
+        return int(self._lib.lsg_workspace_bytes(self._h))
+
+    def set_model(self, model):
+        self._check(self._lib.lsg_set_model(self._h, C.byref(model)))
+
+    # ---- host-buffer calls ---------------------------------------------------------------
+    def match_pairs(self, spans, events, idents, window_ns, threshold, expected_match=None, expected_tier=None):
+        spans, events, idents = _as(spans, A.SPAN_DTYPE), _as(events, A.EVENT_DTYPE), _as(idents, A.IDENT_DTYPE)
+        n = len(spans)
+        assert len(events) == n
+        em, et = _as(expected_match, np.uint8), _as(expected_tier, np.uint8)
+        tier = np.empty(n, np.uint8)
+        pred = np.empty(n, np.uint8)
+        ev = A.Eval()
+        self._check(self._lib.lsg_match_pairs(self._h, _ptr(spans), _ptr(events), n, _ptr(idents), len(idents),
+                                              int(window_ns), float(threshold), _ptr(em), _ptr(et), _ptr(tier),
+                                              _ptr(pred), C.byref(ev)))
+        return tier, pred, ev
+
+    def process_batch(self, spans, events, idents, window_ns=0, threshold=0.0, fanout=0, attr_base=None):
+        spans, events, idents = _as(spans, A.SPAN_DTYPE), _as(events, A.EVENT_DTYPE), _as(idents, A.IDENT_DTYPE)
+        ns, ne = len(spans), len(events)
+        f = fanout if fanout > 0 else 3
+        base = _as(attr_base, np.float64)
+        out = {
+            "cand_event": np.empty((ns, f), np.uint32), "cand_tier": np.empty((ns, f), np.uint8),
+            "attr": np.empty((ns, A.NSIG), np.float64), "conf": np.empty(ns, np.float64),
+            "retrieval": np.empty(ns, np.float64), "n_cand": np.empty(ns, np.uint32),
+        }
+        dbg = A.Debug()
+        self._check(self._lib.lsg_process_batch(self._h, _ptr(spans), ns, _ptr(events), ne, _ptr(idents), len(idents),
+                                                int(window_ns), float(threshold), int(fanout), _ptr(base),
+                                                _ptr(out["cand_event"]), _ptr(out["cand_tier"]), _ptr(out["attr"]),
+                                                _ptr(out["conf"]), _ptr(out["retrieval"]), _ptr(out["n_cand"]),
+                                                C.byref(dbg)))
+        out["debug"] = dbg
+        return out
+
+    def incident_features(self, span_attr, span_incident, n_incidents, want_features=False):
+        span_attr = _as(span_attr, np.float64)
+        span_incident = _as(span_incident, np.uint32)
+        ns = len(span_incident)
+        sig = np.empty((n_incidents, A.NSIG), np.float64)
+        feat = np.zeros((n_incidents, A.NSIG), A.FEATURE_DTYPE) if want_features else None
+        self._check(self._lib.lsg_incident_features(self._h, _ptr(span_attr), _ptr(span_incident), ns, n_incidents,
+                                                    _ptr(sig), _ptr(feat)))
+        return (sig, feat) if want_features else sig
+
+    def attribute(self, signals, has_signals=None, rule_label=None):
+        signals = _as(signals, np.float64).reshape(-1, A.NSIG)
+        n = len(signals)
+        hs, rl = _as(has_signals, np.uint8), _as(rule_label, np.uint8)
+        post = np.empty((n, A.NDOM), np.float64)
+        top1 = np.empty(n, np.uint8)
+        elev = np.empty(n, np.uint16)
+        self._check(self._lib.lsg_attribute(self._h, _ptr(signals), _ptr(hs), _ptr(rl), n, _ptr(post), _ptr(top1),
+                                            _ptr(elev)))
+        return post, top1, elev
+
+    def confusion(self, actual, predicted, expected, expected_n, posterior, coverage_thr, hyp_floor=0.0):
+        actual, predicted = _as(actual, np.uint8), _as(predicted, np.uint8)
+        expected, expected_n = _as(expected, np.uint32), _as(expected_n, np.uint8)
+        posterior = _as(posterior, np.float64)
+        out = A.ConfusionOut()
+        self._check(self._lib.lsg_confusion(self._h, _ptr(actual), _ptr(predicted), _ptr(expected), _ptr(expected_n),
+                                            _ptr(posterior), float(coverage_thr), float(hyp_floor), len(actual),
+                                            C.byref(out)))
+        return out
+
+    # ---- device-pointer calls (integers are raw device addresses, e.g. torch.Tensor.data_ptr()) ----
+    def call_dev(self, name, *args):
+        self._check(getattr(self._lib, name)(self._h, *args))
+
+
+_DEFAULT = None
+
+
+def default_context():
+    """Process-wide context on device LLMSLO_GPU_DEVICE (default 0), created on first use."""
+    global _DEFAULT
+    if _DEFAULT is None:
+        _DEFAULT = Context(int(os.environ.get("LLMSLO_GPU_DEVICE", "0")))
+    return _DEFAULT
