@@ -144,6 +144,11 @@ uint64_t lsg_launch_count(const lsg_ctx *ctx);
 /* bytes of device workspace currently held */
 size_t lsg_workspace_bytes(const lsg_ctx *ctx);
 
+/* sizeof() of the ABI structs as compiled into the library, in header order (event, span, ident, debug, eval,
+ * model, confusion_out, feature, counters, pipeline_args, synth_cfg); returns how many there are.  Lets a
+ * binding check its own struct mirrors at load time. */
+int lsg_abi_sizes(size_t *out, int n);
+
 /* NewBayesianAttributor() defaults (bayesian.go:46-207) */
 void lsg_default_model(lsg_model *out);
 /* replaces reading b.Priors / b.Likelihoods inside Attribute (bayesian.go:230-242) */
@@ -252,8 +257,20 @@ typedef struct {
   double *inc_signals; double *posterior; uint8_t *top1;
   uint64_t *counters_dev;
 } lsg_pipeline_args;
-/* asynchronous: returns after enqueueing on the context's stream */
+/* asynchronous: returns after enqueueing on the context's stream (it synchronises once inside, after the
+ * first reduction, to read the key layout back) */
 int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *args);
+/* the same with HOST buffers in and out (every pointer of `args` is a host pointer; outputs may be NULL):
+ * copies up, runs, copies back, synchronises.  What ProcessBatch + BuildAttributionsBayes +
+ * BuildConfusionMatrix cost a Go caller end to end (processor.go:29, pipeline.go:31,65). */
+int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *args, lsg_counters *counters_out);
+
+/* ---- per-kernel timing with CUDA events on the context's stream (bench.py's roofline numbers) ---------
+ *  lsg_profile_read synchronises the stream, adds the finished intervals to per-kernel totals and copies
+ *  up to `cap` of them out (milliseconds, launches-groups counted); returns the number of kinds. */
+int lsg_profile_enable(lsg_ctx *ctx, int on);
+const char *lsg_profile_name(int kind);
+int lsg_profile_read(lsg_ctx *ctx, double *ms, uint64_t *count, int cap, int reset);
 
 /* ---- synthetic workload: record i is a pure function of (seed, i), generated on
  *      the device by lsg_synth_dev and on the host by lsg_synth_host with identical results. */

@@ -71,6 +71,11 @@ def load_library():
         lib.lsg_synth_n_incidents.restype = sz
         lib.lsg_synth_dev.argtypes = [vp, P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
         lib.lsg_synth_host.argtypes = [P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
+        lib.lsg_pipeline.argtypes = [vp, P(A.PipelineArgs), P(A.Counters)]
+        lib.lsg_profile_enable.argtypes = [vp, cint]
+        lib.lsg_profile_name.argtypes = [cint]
+        lib.lsg_profile_name.restype = C.c_char_p
+        lib.lsg_profile_read.argtypes = [vp, P(C.c_double), P(C.c_uint64), cint, cint]
         lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
         lib.lsg_abi_sizes.restype = cint
         _LIB = lib
@@ -194,6 +199,18 @@ class Context:
                                             _ptr(posterior), float(coverage_thr), float(hyp_floor), len(actual),
                                             C.byref(out)))
         return out
+
+    def profile_enable(self, on=True):
+        self._check(self._lib.lsg_profile_enable(self._h, 1 if on else 0))
+
+    def profile_read(self, reset=True):
+        """{kernel name: (total ms, intervals)} since the last reset; synchronises the stream."""
+        ms = (C.c_double * 32)()
+        cnt = (C.c_uint64 * 32)()
+        n = self._lib.lsg_profile_read(self._h, ms, cnt, 32, 1 if reset else 0)
+        if n < 0:
+            self._check(n)
+        return {self._lib.lsg_profile_name(i).decode(): (ms[i], int(cnt[i])) for i in range(n)}
 
     # ---- device-pointer calls (integers are raw device addresses, e.g. torch.Tensor.data_ptr()) ----
     def call_dev(self, name, *args):

@@ -1,0 +1,586 @@
+// api.cu — the C ABI of include/llmslo_gpu.h: context, workspace, host-buffer wrappers and the fused
+// device-resident pipeline.  Everything that computes is a CUDA kernel in the sibling .cu files; this
+// file only moves buffers, validates arguments and launches.  No CPU fallback.
+#include <cmath>
+#include <cstdarg>
+#include <new>
+
+#include "common.cuh"
+
+static_assert(sizeof(lsg_event) == 32 && sizeof(lsg_span) == 32 && sizeof(lsg_ident) == 16, "record layout");
+static_assert(sizeof(lsg_feature) == 80, "feature layout");
+
+int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+int lsg_ws(lsg_ctx *ctx, int slot, size_t bytes, void **out) {
+  if (bytes == 0) bytes = 16;
+  if (ctx->ws_cap[slot] < bytes) {
+    if (ctx->ws[slot]) {
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(ctx->ws[slot]);
+      ctx->ws[slot] = nullptr;
+      ctx->ws_cap[slot] = 0;
+    }
+    size_t cap = bytes + bytes / 8;   // headroom so that slowly growing batches do not reallocate every call
+    cap = (cap + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc(&ctx->ws[slot], cap);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return lsg_fail(ctx, LSG_ERR_NOMEM, "cudaMalloc of %zu bytes (workspace slot %d) failed: %s", cap, slot, cudaGetErrorString(e));
+    }
+    ctx->ws_cap[slot] = cap;
+  }
+  *out = ctx->ws[slot];
+  return 0;
+}
+
+namespace {
+
+constexpr size_t SMALL_JOIN = 256, SMALL_EVAL = 512, SMALL_CONF = 1024;
+
+void build_dev_model(const lsg_model *m, DevModel *d) {
+  auto clampl = [](double p) { return p < 0.01 ? 0.01 : (p > 0.99 ? 0.99 : p); };   // bayesian.go:303-311
+  for (int k = 0; k < LSG_NDOM; ++k) {
+    double prior = m->prior[k];
+    if (!(prior > 0)) prior = 1e-10;   // bayesian.go:231-233
+    d->log_prior[k] = std::log(prior);
+    d->log_extra[k] = m->log_extra[k];
+  }
+  for (int s = 0; s < LSG_NSIG; ++s) {
+    d->thresh[s] = m->thresh[s];
+    for (int k = 0; k < LSG_NDOM; ++k) {
+      const double p = m->lik[s][k];
+      if (std::isnan(p)) {   // likelihoodFor: domain missing -> 0.5 (bayesian.go:293-296)
+        d->log_elev[s][k] = d->log_not[s][k] = std::log(0.5);
+      } else {
+        d->log_elev[s][k] = std::log(clampl(p));
+        d->log_not[s][k] = std::log(clampl(1 - p));
+      }
+    }
+  }
+  d->sig_mask = m->sig_mask;
+}
+
+int set_device(lsg_ctx *ctx) {
+  LSG_CUDA(ctx, cudaSetDevice(ctx->device));
+  return 0;
+}
+
+template <typename T>
+int h2d(lsg_ctx *ctx, int slot, const T *host, size_t n, const T **dev) {
+  *dev = nullptr;
+  if (!host) return 0;
+  void *p;
+  LSG_TRY(lsg_ws(ctx, slot, n * sizeof(T), &p));
+  if (n) LSG_CUDA(ctx, cudaMemcpyAsync(p, host, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  *dev = (const T *)p;
+  return 0;
+}
+template <typename T>
+int dalloc(lsg_ctx *ctx, int slot, bool want, size_t n, T **dev) {
+  *dev = nullptr;
+  if (!want) return 0;
+  void *p;
+  LSG_TRY(lsg_ws(ctx, slot, n * sizeof(T), &p));
+  *dev = (T *)p;
+  return 0;
+}
+template <typename T>
+int d2h(lsg_ctx *ctx, T *host, const T *dev, size_t n) {
+  if (host && dev && n) LSG_CUDA(ctx, cudaMemcpyAsync(host, dev, n * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  return 0;
+}
+
+int norm_params(lsg_ctx *ctx, int64_t *window_ns, double *threshold, int *fanout) {
+  if (*window_ns <= 0) *window_ns = 2000 * kMs;            // dns.go:51-53
+  if (*threshold <= 0) *threshold = 0.7;                  // correlator.go:58-61
+  if (fanout && *fanout <= 0) *fanout = 3;                // correlator.go:62-66
+  if (*window_ns > LSG_MAX_WINDOW_NS) return lsg_fail(ctx, LSG_ERR_INVALID, "window_ns %lld exceeds 2^53-1", (long long)*window_ns);
+  if (fanout && *fanout > LSG_MAX_FANOUT) return lsg_fail(ctx, LSG_ERR_INVALID, "fanout %d exceeds LSG_MAX_FANOUT=%d", *fanout, LSG_MAX_FANOUT);
+  return 0;
+}
+
+// sort + join on device pointers; counters_host[0..4] = matched, low_confidence, fanout_dropped, candidates, kept
+int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                       const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
+                       const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
+                       double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted) {
+  LSG_TRY(lsg_sort_events(ctx, events, n_events, idents, n_idents, window_ns, false, nullptr, sorted));
+  const uint32_t *span_perm = nullptr;
+  LSG_TRY(lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm));
+  void *small_v;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  JoinArgs ja;
+  ja.spans = spans; ja.n_spans = n_spans; ja.span_perm = span_perm;
+  ja.ev = *sorted; ja.events_in = events; ja.idents = idents; ja.n_idents = n_idents;
+  ja.window_ns = window_ns; ja.threshold = threshold; ja.fanout = fanout;
+  ja.attr_base = attr_base; ja.cand_event = cand_event; ja.cand_tier = cand_tier; ja.attr_out = attr_out;
+  ja.conf_out = conf_out; ja.retrieval_out = retrieval_out; ja.n_cand_out = n_cand_out;
+  ja.counters = (uint64_t *)((char *)small_v + SMALL_JOIN);
+  LSG_TRY(lsg_launch_join(ctx, ja));
+  *join_counters_dev = ja.counters;
+  return 0;
+}
+
+void fill_debug(lsg_debug *d, const uint64_t *jc, const SortedEvents &sorted, size_t n_spans) {
+  const uint64_t n_supported = (uint64_t)sorted.n - sorted.n_unsupported;
+  d->unsupported_type = sorted.n_unsupported * (uint64_t)n_spans;   // correlator.go:73-77, once per span
+  d->unmatched = n_supported * (uint64_t)n_spans - jc[0];           // every supported pair that did not match
+  d->low_confidence = jc[1];
+  d->fanout_dropped = jc[2];
+}
+
+__global__ void k_finalize_counters(const unsigned long long *__restrict__ jc, unsigned long long n_events,
+                                    unsigned long long n_unsupported, unsigned long long n_spans,
+                                    unsigned long long n_incidents, unsigned long long *__restrict__ out) {
+  // layout = lsg_counters: debug[4] | confusion | events spans incidents candidates kept
+  const int tail = 4 + (int)(sizeof(lsg_confusion_out) / 8);
+  out[0] = (n_events - n_unsupported) * n_spans - jc[0];
+  out[1] = jc[1];
+  out[2] = jc[2];
+  out[3] = n_unsupported * n_spans;
+  out[tail + 0] = n_events;
+  out[tail + 1] = n_spans;
+  out[tail + 2] = n_incidents;
+  out[tail + 3] = jc[3];
+  out[tail + 4] = jc[4];
+}
+
+__global__ void k_widen_keys(const uint32_t *__restrict__ in, size_t n, unsigned long long *__restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = in[i] == 0xffffffffu ? ~0ull : (unsigned long long)in[i];
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *lsg_version(void) { return "llmslo_gpu 0.1 (sm_100a)"; }
+
+int lsg_abi_sizes(size_t *out, int n) {
+  const size_t v[] = {sizeof(lsg_event), sizeof(lsg_span), sizeof(lsg_ident), sizeof(lsg_debug), sizeof(lsg_eval),
+                      sizeof(lsg_model), sizeof(lsg_confusion_out), sizeof(lsg_feature), sizeof(lsg_counters),
+                      sizeof(lsg_pipeline_args), sizeof(lsg_synth_cfg)};
+  const int m = (int)(sizeof v / sizeof v[0]);
+  for (int i = 0; i < n && i < m; ++i) out[i] = v[i];
+  return m;
+}
+
+int lsg_create(int device, void *stream, lsg_ctx **out) {
+  if (!out) return LSG_ERR_INVALID;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0 || device < 0 || device >= count) {
+    cudaGetLastError();
+    return LSG_ERR_NODEVICE;
+  }
+  lsg_ctx *ctx = new (std::nothrow) lsg_ctx();
+  if (!ctx) return LSG_ERR_NOMEM;
+  ctx->device = device;
+  if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return LSG_ERR_NODEVICE; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return LSG_ERR_NODEVICE; }
+  if (prop.major < 10) {   // the kernels are built for sm_100a only
+    delete ctx;
+    return LSG_ERR_NODEVICE;
+  }
+  ctx->sm_count = prop.multiProcessorCount;
+  if (stream) {
+    ctx->stream = (cudaStream_t)stream;
+  } else {
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return LSG_ERR_CUDA; }
+    ctx->own_stream = true;
+  }
+  ctx->pinned_cap = 8192;
+  if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) {
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return LSG_ERR_NOMEM;
+  }
+  lsg_model m;
+  lsg_default_model(&m);
+  build_dev_model(&m, &ctx->model);
+  ctx->model_set = true;
+  *out = ctx;
+  return 0;
+}
+
+void lsg_destroy(lsg_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (int i = 0; i < WS_COUNT; ++i)
+    if (ctx->ws[i]) cudaFree(ctx->ws[i]);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (auto &sp : ctx->prof_open) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+  for (auto e : ctx->prof_pool) cudaEventDestroy(e);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+// ---- per-kernel timing ------------------------------------------------------------------------------
+static const char *kProfNames[PK_COUNT] = {"event_stats", "event_keys", "radix_hist", "radix_scan", "radix_scatter",
+                                           "gather_events", "span_sort", "join", "incident_features", "attribute",
+                                           "confusion", "match_pairs"};
+int lsg_profile_enable(lsg_ctx *ctx, int on) {
+  if (!ctx) return LSG_ERR_INVALID;
+  ctx->prof = on != 0;
+  return 0;
+}
+const char *lsg_profile_name(int kind) { return kind >= 0 && kind < PK_COUNT ? kProfNames[kind] : nullptr; }
+int lsg_profile_read(lsg_ctx *ctx, double *ms, uint64_t *count, int cap, int reset) {
+  if (!ctx) return LSG_ERR_INVALID;
+  LSG_TRY(set_device(ctx));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (auto &sp : ctx->prof_open) {
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess) {
+      ctx->prof_ms[sp.kind] += t;
+      ctx->prof_n[sp.kind]++;
+    }
+    ctx->prof_pool.push_back(sp.a);
+    ctx->prof_pool.push_back(sp.b);
+  }
+  ctx->prof_open.clear();
+  for (int i = 0; i < cap && i < PK_COUNT; ++i) {
+    if (ms) ms[i] = ctx->prof_ms[i];
+    if (count) count[i] = ctx->prof_n[i];
+  }
+  if (reset)
+    for (int i = 0; i < PK_COUNT; ++i) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
+  return PK_COUNT;
+}
+
+const char *lsg_last_error(const lsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+uint64_t lsg_launch_count(const lsg_ctx *ctx) { return ctx ? ctx->launches : 0; }
+size_t lsg_workspace_bytes(const lsg_ctx *ctx) {
+  size_t t = 0;
+  if (ctx) for (int i = 0; i < WS_COUNT; ++i) t += ctx->ws_cap[i];
+  return t;
+}
+
+void lsg_default_model(lsg_model *m) {
+  // DefaultPriors / DefaultLikelihoods / signalThresholds, bayesian.go:54-207
+  static const double lik[LSG_NSIG][LSG_NDOM] = {
+      {0.95, 0.70, 0.10, 0.10, 0.10, 0.10, 0.15, 0.10},   // dns_latency_ms
+      {0.15, 0.90, 0.10, 0.10, 0.10, 0.15, 0.10, 0.10},   // tcp_retransmits_total
+      {0.10, 0.10, 0.90, 0.60, 0.10, 0.10, 0.10, 0.10},   // runqueue_delay_ms
+      {0.50, 0.85, 0.10, 0.10, 0.75, 0.40, 0.30, 0.10},   // connect_latency_ms
+      {0.10, 0.30, 0.10, 0.10, 0.80, 0.50, 0.20, 0.10},   // tls_handshake_ms
+      {0.10, 0.10, 0.90, 0.20, 0.10, 0.10, 0.10, 0.10},   // cpu_steal_pct
+      {0.10, 0.10, 0.85, 0.75, 0.10, 0.10, 0.10, 0.10},   // cfs_throttled_ms
+      {0.05, 0.05, 0.15, 0.95, 0.05, 0.05, 0.05, 0.05},   // mem_reclaim_latency_ms
+      {0.05, 0.05, 0.10, 0.85, 0.05, 0.05, 0.30, 0.05},   // disk_io_latency_ms
+      {0.10, 0.20, 0.15, 0.10, 0.90, 0.60, 0.40, 0.10},   // syscall_latency_ms
+      {0.10, 0.80, 0.05, 0.05, 0.60, 0.85, 0.15, 0.10},   // connect_errors_total
+      {0.05, 0.70, 0.05, 0.05, 0.30, 0.60, 0.10, 0.05}};  // tls_handshake_fail_total
+  static const double thr[LSG_NSIG] = {40, 2, 10, 80, 60, 2, 40, 5, 10, 50, 1, 1};
+  memset(m, 0, sizeof *m);
+  for (int d = 0; d < LSG_NDOM; ++d) m->prior[d] = 1.0 / (double)LSG_NDOM;
+  memcpy(m->lik, lik, sizeof lik);
+  memcpy(m->thresh, thr, sizeof thr);
+  m->sig_mask = (1u << LSG_NSIG) - 1;
+}
+
+int lsg_set_model(lsg_ctx *ctx, const lsg_model *model) {
+  if (!ctx || !model) return LSG_ERR_INVALID;
+  build_dev_model(model, &ctx->model);
+  ctx->model_set = true;
+  return 0;
+}
+
+// ---- A2-A3 ----------------------------------------------------------------------------------------
+int lsg_match_pairs_dev(lsg_ctx *ctx, const lsg_span *spans, const lsg_event *events, size_t n, const lsg_ident *idents,
+                        size_t n_idents, int64_t window_ns, double threshold, const uint8_t *expected_match,
+                        const uint8_t *expected_tier, uint8_t *tier_out, uint8_t *predicted_out, lsg_eval *eval_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (n && (!spans || !events || !idents || !tier_out || !predicted_out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  LSG_TRY(norm_params(ctx, &window_ns, &threshold, nullptr));
+  void *small_v;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  uint64_t *eval_dev = (uint64_t *)((char *)small_v + SMALL_EVAL);
+  LSG_TRY(lsg_launch_match_pairs(ctx, spans, events, n, idents, n_idents, window_ns, threshold, expected_match, expected_tier,
+                                 tier_out, predicted_out, eval_dev));
+  uint64_t *pin = (uint64_t *)ctx->pinned;
+  const size_t words = sizeof(lsg_eval) / 8 + 1;
+  LSG_CUDA(ctx, cudaMemcpyAsync(pin, eval_dev, words * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (pin[words - 1] & 0xffffffffu) return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if (eval_out) memcpy(eval_out, pin, sizeof(lsg_eval));
+  return 0;
+}
+
+int lsg_match_pairs(lsg_ctx *ctx, const lsg_span *spans, const lsg_event *events, size_t n, const lsg_ident *idents,
+                    size_t n_idents, int64_t window_ns, double threshold, const uint8_t *expected_match,
+                    const uint8_t *expected_tier, uint8_t *tier_out, uint8_t *predicted_out, lsg_eval *eval_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (n && (!spans || !events || !idents || !tier_out || !predicted_out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  const lsg_span *d_sp; const lsg_event *d_ev; const lsg_ident *d_id; const uint8_t *d_em, *d_et;
+  LSG_TRY(h2d(ctx, WS_SPANS_IN, spans, n, &d_sp));
+  LSG_TRY(h2d(ctx, WS_EVENTS_IN, events, n, &d_ev));
+  LSG_TRY(h2d(ctx, WS_IDENTS, idents, n_idents, &d_id));
+  LSG_TRY(h2d(ctx, WS_IN0, expected_match, n, &d_em));
+  LSG_TRY(h2d(ctx, WS_IN1, expected_tier, n, &d_et));
+  uint8_t *d_tier, *d_pred;
+  LSG_TRY(dalloc(ctx, WS_OUT0, true, n, &d_tier));
+  LSG_TRY(dalloc(ctx, WS_OUT1, true, n, &d_pred));
+  // kernel, then results; lsg_match_pairs_dev synchronises after reading the counters back
+  int rc = lsg_match_pairs_dev(ctx, d_sp, d_ev, n, d_id, n_idents, window_ns, threshold, d_em, d_et, d_tier, d_pred, eval_out);
+  if (rc) return rc;
+  LSG_TRY(d2h(ctx, tier_out, (const uint8_t *)d_tier, n));
+  LSG_TRY(d2h(ctx, predicted_out, (const uint8_t *)d_pred, n));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- A4-A6 ----------------------------------------------------------------------------------------
+int lsg_process_batch_dev(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                          const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
+                          const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
+                          double *retrieval_out, uint32_t *n_cand_out, lsg_debug *debug_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n_spans && (!spans || !cand_event || !cand_tier || !attr_out || !conf_out)) || (n_events && !events) ||
+      ((n_spans || n_events) && !idents))
+    return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  LSG_TRY(norm_params(ctx, &window_ns, &threshold, &fanout));
+  uint64_t *jc_dev = nullptr;
+  SortedEvents sorted;
+  LSG_TRY(process_batch_core(ctx, spans, n_spans, events, n_events, idents, n_idents, window_ns, threshold, fanout, attr_base,
+                             cand_event, cand_tier, attr_out, conf_out, retrieval_out, n_cand_out, &jc_dev, &sorted));
+  uint64_t *pin = (uint64_t *)ctx->pinned;
+  LSG_CUDA(ctx, cudaMemcpyAsync(pin, jc_dev, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (pin[5]) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if (debug_out) fill_debug(debug_out, pin, sorted, n_spans);
+  return 0;
+}
+
+int lsg_process_batch(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                      const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
+                      const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
+                      double *retrieval_out, uint32_t *n_cand_out, lsg_debug *debug_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n_spans && (!spans || !cand_event || !cand_tier || !attr_out || !conf_out)) || (n_events && !events) ||
+      ((n_spans || n_events) && !idents))
+    return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  int f = fanout <= 0 ? 3 : fanout;
+  const lsg_span *d_sp; const lsg_event *d_ev; const lsg_ident *d_id; const double *d_base;
+  LSG_TRY(h2d(ctx, WS_SPANS_IN, spans, n_spans, &d_sp));
+  LSG_TRY(h2d(ctx, WS_EVENTS_IN, events, n_events, &d_ev));
+  LSG_TRY(h2d(ctx, WS_IDENTS, idents, n_idents, &d_id));
+  LSG_TRY(h2d(ctx, WS_IN0, attr_base, n_spans * LSG_NSIG, &d_base));
+  uint32_t *d_ce, *d_nc; uint8_t *d_ct; double *d_attr, *d_conf, *d_ret;
+  LSG_TRY(dalloc(ctx, WS_OUT0, true, n_spans * f, &d_ce));
+  LSG_TRY(dalloc(ctx, WS_OUT1, true, n_spans * f, &d_ct));
+  LSG_TRY(dalloc(ctx, WS_OUT2, true, n_spans * LSG_NSIG, &d_attr));
+  LSG_TRY(dalloc(ctx, WS_OUT3, true, n_spans, &d_conf));
+  LSG_TRY(dalloc(ctx, WS_OUT4, retrieval_out != nullptr, n_spans, &d_ret));
+  LSG_TRY(dalloc(ctx, WS_OUT5, n_cand_out != nullptr, n_spans, &d_nc));
+  int rc = lsg_process_batch_dev(ctx, d_sp, n_spans, d_ev, n_events, d_id, n_idents, window_ns, threshold, fanout, d_base, d_ce,
+                                 d_ct, d_attr, d_conf, d_ret, d_nc, debug_out);
+  if (rc) return rc;
+  LSG_TRY(d2h(ctx, cand_event, (const uint32_t *)d_ce, n_spans * f));
+  LSG_TRY(d2h(ctx, cand_tier, (const uint8_t *)d_ct, n_spans * f));
+  LSG_TRY(d2h(ctx, attr_out, (const double *)d_attr, n_spans * LSG_NSIG));
+  LSG_TRY(d2h(ctx, conf_out, (const double *)d_conf, n_spans));
+  LSG_TRY(d2h(ctx, retrieval_out, (const double *)d_ret, n_spans));
+  LSG_TRY(d2h(ctx, n_cand_out, (const uint32_t *)d_nc, n_spans));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int lsg_sort_events_dev(lsg_ctx *ctx, const lsg_event *events, size_t n_events, const lsg_ident *idents, size_t n_idents,
+                        lsg_event *sorted_out, uint32_t *perm_out, uint64_t *keys_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (n_events && (!events || !idents || !sorted_out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  SortedEvents sorted;
+  LSG_TRY(lsg_sort_events(ctx, events, n_events, idents, n_idents, 0, true, sorted_out, &sorted));
+  if (n_events && perm_out)
+    LSG_CUDA(ctx, cudaMemcpyAsync(perm_out, sorted.perm, n_events * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  if (n_events && keys_out) {
+    if (sorted.key.bits <= 31) {   // short keys are sorted as 32-bit words; the ABI always hands out 64-bit keys
+      k_widen_keys<<<(unsigned)((n_events + 255) / 256 > 4096 ? 4096 : (n_events + 255) / 256), 256, 0, ctx->stream>>>(
+          (const uint32_t *)sorted.keys, n_events, (unsigned long long *)keys_out);
+      LSG_LAUNCH_CHECK(ctx);
+    } else {
+      LSG_CUDA(ctx, cudaMemcpyAsync(keys_out, sorted.keys, n_events * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+  }
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- A7 -------------------------------------------------------------------------------------------
+int lsg_incident_features_dev(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
+                              size_t n_incidents, double *signals_out, lsg_feature *features_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n_spans && (!span_attr || !span_incident)) || (n_incidents && !signals_out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  LSG_TRY(lsg_launch_incident_features(ctx, span_attr, span_incident, nullptr, n_spans, n_incidents, signals_out, features_out));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int lsg_incident_features(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
+                          size_t n_incidents, double *signals_out, lsg_feature *features_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n_spans && (!span_attr || !span_incident)) || (n_incidents && !signals_out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  const double *d_attr; const uint32_t *d_inc;
+  LSG_TRY(h2d(ctx, WS_IN0, span_attr, n_spans * LSG_NSIG, &d_attr));
+  LSG_TRY(h2d(ctx, WS_IN1, span_incident, n_spans, &d_inc));
+  double *d_sig; lsg_feature *d_feat;
+  LSG_TRY(dalloc(ctx, WS_OUT0, true, n_incidents * LSG_NSIG, &d_sig));
+  LSG_TRY(dalloc(ctx, WS_OUT1, features_out != nullptr, n_incidents * LSG_NSIG, &d_feat));
+  LSG_TRY(lsg_launch_incident_features(ctx, d_attr, d_inc, nullptr, n_spans, n_incidents, d_sig, d_feat));
+  LSG_TRY(d2h(ctx, signals_out, (const double *)d_sig, n_incidents * LSG_NSIG));
+  LSG_TRY(d2h(ctx, features_out, (const lsg_feature *)d_feat, n_incidents * LSG_NSIG));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- A9-A10 ---------------------------------------------------------------------------------------
+int lsg_attribute_dev(lsg_ctx *ctx, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
+                      double *posterior, uint8_t *top1, uint16_t *elev_mask) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (n && (!signals || !posterior || !top1)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  LSG_TRY(lsg_launch_attribute(ctx, signals, has_signals, rule_label, n, posterior, top1, elev_mask));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int lsg_attribute(lsg_ctx *ctx, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
+                  double *posterior, uint8_t *top1, uint16_t *elev_mask) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (n && (!signals || !posterior || !top1)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  const double *d_sig; const uint8_t *d_has, *d_rule;
+  LSG_TRY(h2d(ctx, WS_IN0, signals, n * LSG_NSIG, &d_sig));
+  LSG_TRY(h2d(ctx, WS_IN1, has_signals, n, &d_has));
+  LSG_TRY(h2d(ctx, WS_IN2, rule_label, n, &d_rule));
+  double *d_post; uint8_t *d_top; uint16_t *d_elev;
+  LSG_TRY(dalloc(ctx, WS_OUT0, true, n * LSG_NDOM, &d_post));
+  LSG_TRY(dalloc(ctx, WS_OUT1, true, n, &d_top));
+  LSG_TRY(dalloc(ctx, WS_OUT2, elev_mask != nullptr, n, &d_elev));
+  LSG_TRY(lsg_launch_attribute(ctx, d_sig, d_has, d_rule, n, d_post, d_top, d_elev));
+  LSG_TRY(d2h(ctx, posterior, (const double *)d_post, n * LSG_NDOM));
+  LSG_TRY(d2h(ctx, top1, (const uint8_t *)d_top, n));
+  LSG_TRY(d2h(ctx, elev_mask, (const uint16_t *)d_elev, n));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+// ---- A12-A13 --------------------------------------------------------------------------------------
+int lsg_confusion_dev(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted, const uint32_t *expected,
+                      const uint8_t *expected_n, const double *posterior, double coverage_thr, double hyp_floor, size_t n,
+                      lsg_confusion_out *out) {
+  if (!ctx || !out) return LSG_ERR_INVALID;
+  if (n && (!actual || !predicted || !expected || !expected_n)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  void *small_v;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  uint64_t *conf_dev = (uint64_t *)((char *)small_v + SMALL_CONF);
+  LSG_CUDA(ctx, cudaMemsetAsync(conf_dev, 0, sizeof(lsg_confusion_out), ctx->stream));
+  LSG_TRY(lsg_launch_confusion(ctx, actual, predicted, expected, expected_n, posterior, coverage_thr, hyp_floor, n, conf_dev));
+  LSG_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, conf_dev, sizeof(lsg_confusion_out), cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(out, ctx->pinned, sizeof(lsg_confusion_out));
+  return 0;
+}
+
+int lsg_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted, const uint32_t *expected,
+                  const uint8_t *expected_n, const double *posterior, double coverage_thr, double hyp_floor, size_t n,
+                  lsg_confusion_out *out) {
+  if (!ctx || !out) return LSG_ERR_INVALID;
+  if (n && (!actual || !predicted || !expected || !expected_n)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  const uint8_t *d_a, *d_p, *d_en; const uint32_t *d_e; const double *d_post;
+  LSG_TRY(h2d(ctx, WS_IN0, actual, n, &d_a));
+  LSG_TRY(h2d(ctx, WS_IN1, predicted, n, &d_p));
+  LSG_TRY(h2d(ctx, WS_IN2, expected, n, &d_e));
+  LSG_TRY(h2d(ctx, WS_IN3, expected_n, n, &d_en));
+  LSG_TRY(h2d(ctx, WS_IN4, posterior, n * LSG_NDOM, &d_post));
+  return lsg_confusion_dev(ctx, d_a, d_p, d_e, d_en, d_post, coverage_thr, hyp_floor, n, out);
+}
+
+// ---- the whole hot path, device resident ------------------------------------------------------------
+int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
+  if (!ctx || !a) return LSG_ERR_INVALID;
+  if (!a->spans || !a->events || !a->idents || !a->cand_event || !a->cand_tier || !a->attr_out || !a->conf_out ||
+      !a->inc_signals || !a->posterior || !a->top1 || !a->counters_dev || !a->inc_actual || !a->inc_expected ||
+      !a->inc_expected_n)
+    return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  int64_t window_ns = a->window_ns;
+  double threshold = a->threshold;
+  int fanout = a->fanout;
+  LSG_TRY(norm_params(ctx, &window_ns, &threshold, &fanout));
+  LSG_CUDA(ctx, cudaMemsetAsync(a->counters_dev, 0, sizeof(lsg_counters), ctx->stream));
+  uint64_t *jc_dev = nullptr;
+  SortedEvents sorted;
+  LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, a->events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
+                             fanout, nullptr, a->cand_event, a->cand_tier, a->attr_out, a->conf_out, nullptr, nullptr, &jc_dev,
+                             &sorted));
+  LSG_TRY(lsg_launch_incident_features(ctx, a->attr_out, nullptr, a->spans, a->n_spans, a->n_incidents, a->inc_signals, nullptr));
+  LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
+  LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
+                               0.01, a->n_incidents, a->counters_dev + 4));
+  k_finalize_counters<<<1, 1, 0, ctx->stream>>>((const unsigned long long *)jc_dev, a->n_events, sorted.n_unsupported, a->n_spans,
+                                                a->n_incidents, (unsigned long long *)a->counters_dev);
+  LSG_LAUNCH_CHECK(ctx);
+  return 0;
+}
+
+// host-buffer form of the whole path (bench.py's e2e): every pointer of `a` is a HOST pointer (pinned memory
+// makes the copies asynchronous); inputs go up, the pipeline runs, results come back, then it synchronises.
+int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counters_out) {
+  if (!ctx || !a) return LSG_ERR_INVALID;
+  if (!a->spans || !a->events || !a->idents || !a->inc_actual || !a->inc_expected || !a->inc_expected_n)
+    return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  LSG_TRY(set_device(ctx));
+  const int f = a->fanout <= 0 ? 3 : a->fanout;
+  lsg_pipeline_args d = *a;
+  LSG_TRY(h2d(ctx, WS_SPANS_IN, a->spans, a->n_spans, &d.spans));
+  LSG_TRY(h2d(ctx, WS_EVENTS_IN, a->events, a->n_events, &d.events));
+  LSG_TRY(h2d(ctx, WS_IDENTS, a->idents, a->n_idents, &d.idents));
+  LSG_TRY(h2d(ctx, WS_IN0, a->inc_actual, a->n_incidents, &d.inc_actual));
+  LSG_TRY(h2d(ctx, WS_IN1, a->inc_expected, a->n_incidents, &d.inc_expected));
+  LSG_TRY(h2d(ctx, WS_IN2, a->inc_expected_n, a->n_incidents, &d.inc_expected_n));
+  LSG_TRY(dalloc(ctx, WS_OUT0, true, a->n_spans * f, &d.cand_event));
+  LSG_TRY(dalloc(ctx, WS_OUT1, true, a->n_spans * f, &d.cand_tier));
+  LSG_TRY(dalloc(ctx, WS_OUT2, true, a->n_spans * LSG_NSIG, &d.attr_out));
+  LSG_TRY(dalloc(ctx, WS_OUT3, true, a->n_spans, &d.conf_out));
+  LSG_TRY(dalloc(ctx, WS_OUT4, true, a->n_incidents * LSG_NSIG, &d.inc_signals));
+  LSG_TRY(dalloc(ctx, WS_OUT5, true, a->n_incidents * LSG_NDOM, &d.posterior));
+  LSG_TRY(dalloc(ctx, WS_IN3, true, a->n_incidents, &d.top1));
+  LSG_TRY(dalloc(ctx, WS_IN4, true, (size_t)LSG_COUNTER_WORDS, &d.counters_dev));
+  LSG_TRY(lsg_pipeline_dev(ctx, &d));
+  LSG_TRY(d2h(ctx, a->cand_event, (const uint32_t *)d.cand_event, a->n_spans * f));
+  LSG_TRY(d2h(ctx, a->cand_tier, (const uint8_t *)d.cand_tier, a->n_spans * f));
+  LSG_TRY(d2h(ctx, a->attr_out, (const double *)d.attr_out, a->n_spans * LSG_NSIG));
+  LSG_TRY(d2h(ctx, a->conf_out, (const double *)d.conf_out, a->n_spans));
+  LSG_TRY(d2h(ctx, a->inc_signals, (const double *)d.inc_signals, a->n_incidents * LSG_NSIG));
+  LSG_TRY(d2h(ctx, a->posterior, (const double *)d.posterior, a->n_incidents * LSG_NDOM));
+  LSG_TRY(d2h(ctx, a->top1, (const uint8_t *)d.top1, a->n_incidents));
+  LSG_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d.counters_dev, sizeof(lsg_counters), cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (counters_out) memcpy(counters_out, ctx->pinned, sizeof(lsg_counters));
+  if (a->counters_dev) memcpy(a->counters_dev, ctx->pinned, sizeof(lsg_counters));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,232 @@
+// common.cuh — context, workspace, error plumbing and device helpers shared by the kernels of
+// libllmslo_gpu.so.  sm_100a only; no CPU fallback anywhere in this library.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/llmslo_gpu.h"
+
+// ---- workspace slots (grow-only device buffers owned by the context) ---------------------------
+enum {
+  WS_EVENTS_IN = 0,  // host-API staging: events
+  WS_SPANS_IN,       // host-API staging: spans
+  WS_IDENTS,         // host-API staging: identity table
+  WS_KEYS_A,         // radix sort: key ping
+  WS_KEYS_B,         // radix sort: key pong
+  WS_IDX_A,          // radix sort: index ping
+  WS_IDX_B,          // radix sort: index pong
+  WS_HIST,           // radix sort: per-tile digit histograms
+  WS_SMALL,          // reductions / counters / digit bases (a few KB)
+  WS_EV_SORTED,      // events in (grp, time) order
+  WS_SPAN_KEYS_A,
+  WS_SPAN_KEYS_B,
+  WS_SPAN_IDX_A,
+  WS_SPAN_IDX_B,
+  WS_OUT0,           // host-API staging of outputs
+  WS_OUT1,
+  WS_OUT2,
+  WS_OUT3,
+  WS_OUT4,
+  WS_OUT5,
+  WS_IN0,            // host-API staging of misc inputs
+  WS_IN1,
+  WS_IN2,
+  WS_IN3,
+  WS_IN4,
+  WS_FEAT,           // incident feature accumulators
+  WS_COUNT
+};
+
+// device copy of the model: logs are taken on the host (std::log, the oracle's libm) so that the
+// per-domain sums are bit-identical to the CPU restatement; the kernel only adds (bayesian.go:230-242).
+struct DevModel {
+  double log_prior[LSG_NDOM];          // log(prior or 1e-10) + log_extra
+  double log_elev[LSG_NSIG][LSG_NDOM];  // log clamp(p)      (0 if the signal is not in Likelihoods)
+  double log_not[LSG_NSIG][LSG_NDOM];   // log clamp(1 - p)
+  double log_extra[LSG_NDOM];
+  double thresh[LSG_NSIG];
+  uint32_t sig_mask;
+};
+
+// per-kernel timing (bench.py's roofline): CUDA events recorded on the context's stream around each launch
+enum {
+  PK_STATS = 0, PK_KEYS, PK_HIST, PK_SCAN, PK_SCATTER, PK_GATHER, PK_SPAN_SORT, PK_JOIN, PK_FEATURES, PK_ATTRIBUTE,
+  PK_CONFUSION, PK_PAIRS, PK_COUNT
+};
+struct ProfSpan { int kind; cudaEvent_t a, b; };
+
+struct lsg_ctx {
+  bool prof = false;
+  std::vector<ProfSpan> prof_open;      // recorded, not yet collected
+  std::vector<cudaEvent_t> prof_pool;   // reusable events
+  double prof_ms[PK_COUNT] = {};
+  uint64_t prof_n[PK_COUNT] = {};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  std::string err;
+  uint64_t launches = 0;
+  void *ws[WS_COUNT] = {};
+  size_t ws_cap[WS_COUNT] = {};
+  void *pinned = nullptr;  // small pinned readback buffer
+  size_t pinned_cap = 0;
+  DevModel model;
+  bool model_set = false;
+};
+
+int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...);
+int lsg_ws(lsg_ctx *ctx, int slot, size_t bytes, void **out);
+
+#define LSG_CUDA(ctx, call)                                                                            \
+  do {                                                                                                 \
+    cudaError_t e__ = (call);                                                                          \
+    if (e__ != cudaSuccess)                                                                            \
+      return lsg_fail(ctx, LSG_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+#define LSG_TRY(expr)          \
+  do {                         \
+    int rc__ = (expr);         \
+    if (rc__ != 0) return rc__; \
+  } while (0)
+#define LSG_LAUNCH_CHECK(ctx)      \
+  do {                             \
+    (ctx)->launches++;             \
+    LSG_CUDA(ctx, cudaGetLastError()); \
+  } while (0)
+
+// scoped timer: records an event pair around the launches issued while it is alive (only when profiling)
+struct ProfScope {
+  lsg_ctx *ctx; int kind; cudaEvent_t a = nullptr, b = nullptr;
+  ProfScope(lsg_ctx *c, int k) : ctx(c), kind(k) {
+    if (!ctx->prof) return;
+    auto take = [&]() { cudaEvent_t e = nullptr; if (!ctx->prof_pool.empty()) { e = ctx->prof_pool.back(); ctx->prof_pool.pop_back(); } else cudaEventCreate(&e); return e; };
+    a = take(); b = take();
+    cudaEventRecord(a, ctx->stream);
+  }
+  ~ProfScope() {
+    if (!a) return;
+    cudaEventRecord(b, ctx->stream);
+    ctx->prof_open.push_back(ProfSpan{kind, a, b});
+  }
+};
+
+// ---- device helpers ---------------------------------------------------------------------------
+#define LSG_HD __host__ __device__ __forceinline__
+
+static constexpr int64_t kMs = 1000000;
+
+// |a - b| as an exact unsigned magnitude (dns.go:111 compares |float64(a.Sub(b))| <= float64(window);
+// identical for window < 2^53 ns, which the API enforces).
+LSG_HD uint64_t lsg_absdiff(int64_t a, int64_t b) { return a > b ? (uint64_t)a - (uint64_t)b : (uint64_t)b - (uint64_t)a; }
+
+// correlation.Match (dns.go:50-76) on interned records, given |dt| and that neither time is zero and
+// |dt| <= window already holds.  si/ei are the identity rows.  Returns the tier.
+LSG_HD int lsg_match_tier(uint64_t adt, uint32_t s_trace, uint32_t s_pid, uint32_t s_conn, const lsg_ident &si,
+                          uint32_t e_trace, uint32_t e_pid, uint32_t e_conn, const lsg_ident &ei) {
+  if (s_trace != 0 && s_trace == e_trace) return LSG_TIER_TRACE;                       // dns.go:58-60
+  const bool same_pod = si.pod != 0 && si.pod == ei.pod;
+  if (same_pod && s_pid > 0 && s_pid == e_pid && adt <= (uint64_t)(100 * kMs)) return LSG_TIER_POD_PID;    // dns.go:61-64
+  if (same_pod && s_conn != 0 && s_conn == e_conn && adt <= (uint64_t)(250 * kMs)) return LSG_TIER_POD_CONN;  // dns.go:65-68
+  if (si.service != 0 && si.service == ei.service && si.node != 0 && si.node == ei.node &&
+      adt <= (uint64_t)(500 * kMs))
+    return LSG_TIER_SVC_NODE;                                                          // dns.go:69-73
+  return LSG_TIER_NONE;
+}
+
+LSG_HD double lsg_tier_conf(int tier) {
+  return tier == 1 ? 1.0 : tier == 2 ? 0.9 : tier == 3 ? 0.8 : tier == 4 ? 0.65 : 0.0;
+}
+
+#ifdef __CUDACC__
+// 128-bit streaming loads/stores of the 32-byte records (two per record)
+__device__ __forceinline__ uint4 ld_nc_v4(const void *p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld_v4(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
+__device__ __forceinline__ void st_v4(void *p, uint4 v) { *reinterpret_cast<uint4 *>(p) = v; }
+
+struct EventRec {  // register image of an lsg_event
+  int64_t ts;
+  double value;
+  uint32_t ident, pid, conn, trace_sig;
+};
+__device__ __forceinline__ EventRec load_event(const lsg_event *p) {
+  uint4 a = ld_v4(p), b = ld_v4(reinterpret_cast<const uint4 *>(p) + 1);
+  EventRec r;
+  r.ts = (int64_t)(((uint64_t)a.y << 32) | a.x);
+  r.value = __longlong_as_double((long long)(((uint64_t)a.w << 32) | a.z));
+  r.ident = b.x; r.pid = b.y; r.conn = b.z; r.trace_sig = b.w;
+  return r;
+}
+struct SpanRec {
+  int64_t ts;
+  uint32_t ident, pid, conn, trace, incident;
+};
+__device__ __forceinline__ SpanRec load_span(const lsg_span *p) {
+  uint4 a = ld_v4(p), b = ld_v4(reinterpret_cast<const uint4 *>(p) + 1);
+  SpanRec r;
+  r.ts = (int64_t)(((uint64_t)a.y << 32) | a.x);
+  r.ident = a.z; r.pid = a.w; r.conn = b.x; r.trace = b.y; r.incident = b.z;
+  return r;
+}
+__device__ __forceinline__ lsg_ident load_ident(const lsg_ident *t, uint32_t row) {
+  uint4 a = __ldg(reinterpret_cast<const uint4 *>(t + row));
+  lsg_ident r;
+  r.pod = a.x; r.node = a.y; r.service = a.z; r.grp = a.w;
+  return r;
+}
+#endif
+
+// ---- sort key: (join group, quantised time) ------------------------------------------------------
+// live key = (grp << tbits) | ((ts - ts_min) >> shift); records that can match nothing (group 0, zero
+// Time, unsupported signal type) get the all-ones key and sort behind everything a span ever searches.
+struct KeySpec {
+  int64_t ts_min;
+  uint32_t shift;   // time quantum = 2^shift ns
+  uint32_t tbits;   // bits of the quantised time
+  uint32_t bits;    // total key bits (gbits + tbits)
+};
+LSG_HD uint64_t lsg_make_key(const KeySpec &k, uint32_t grp, int64_t ts) {
+  return ((uint64_t)grp << k.tbits) | (((uint64_t)ts - (uint64_t)k.ts_min) >> k.shift);
+}
+
+// stage kernels (defined across the .cu files)
+int lsg_launch_match_pairs(lsg_ctx *, const lsg_span *, const lsg_event *, size_t, const lsg_ident *, size_t, int64_t, double,
+                           const uint8_t *, const uint8_t *, uint8_t *, uint8_t *, uint64_t *eval_dev);
+struct SortedEvents {
+  const lsg_event *rec;   // events in key order
+  const uint32_t *perm;   // sorted position -> input index
+  const void *keys;       // sorted keys (uint32_t if key.bits <= 32 else uint64_t)
+  KeySpec key;
+  size_t n;               // all events
+  size_t n_live;          // events that can match (sorted first)
+  uint64_t n_unsupported; // events with an unsupported signal type
+};
+int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
+                    bool exact, lsg_event *sorted_out, SortedEvents *out);
+int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,
+                   const uint32_t **perm_out);
+struct JoinArgs {
+  const lsg_span *spans; size_t n_spans; const uint32_t *span_perm;
+  SortedEvents ev; const lsg_event *events_in; const lsg_ident *idents; size_t n_idents;
+  int64_t window_ns; double threshold; int fanout;
+  const double *attr_base; uint32_t *cand_event; uint8_t *cand_tier; double *attr_out; double *conf_out;
+  double *retrieval_out; uint32_t *n_cand_out;
+  uint64_t *counters;  // device: [0] matched pairs, [1] low_confidence, [2] fanout_dropped, [3] candidates, [4] kept
+};
+int lsg_launch_join(lsg_ctx *, const JoinArgs &);
+int lsg_launch_incident_features(lsg_ctx *, const double *span_attr, const uint32_t *span_incident, const lsg_span *spans,
+                                 size_t n_spans, size_t n_incidents, double *signals_out, lsg_feature *features_out);
+int lsg_launch_attribute(lsg_ctx *, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
+                         double *posterior, uint8_t *top1, uint16_t *elev_mask);
+int lsg_launch_confusion(lsg_ctx *, const uint8_t *actual, const uint8_t *predicted, const uint32_t *expected,
+                         const uint8_t *expected_n, const double *posterior, double coverage_thr, double hyp_floor, size_t n,
+                         uint64_t *out_dev /* lsg_confusion_out layout, zeroed by the caller */);

@@ -1,0 +1,488 @@
+// sort.cu — K-sort: stable LSD radix sort of events (and spans) by (join group, quantised time).
+//
+// What the reference does here: nothing — ProcessBatch loops every span over every signal
+// (ebpfcorrelator/processor.go:29-49, correlator.go:72-90).  The sort is how this library reaches the
+// same match sets in O(E log E + S*w) instead of O(S*E).
+//
+// Layout in HBM.  The 32-byte records are not moved during the passes: the passes permute
+// (key, index) pairs — 8 bytes per event when the key fits 32 bits, 12 otherwise — and one gather at
+// the end writes the records in key order.  Keys are (grp << tbits) | ((ts - ts_min) >> shift):
+// the join never needs a total order in time (it selects candidates by an explicit
+// (tier, |dt|, input index) order), only that a span's window is a contiguous range, so the time
+// quantum 2^shift is chosen as large as the window allows (<= window/64) and the key shrinks from
+// ~50 bits to 24-32: 3-4 radix passes instead of 6-7.  `exact` (lsg_sort_events_dev) uses shift 0.
+//
+// Each pass = per-tile digit histogram -> per-digit scan over tiles -> stable scatter.  Ranking inside
+// a tile is warp-synchronous (__match_any_sync, one shared-memory counter row per warp), items are
+// staged in shared memory in digit order so that the global writes are coalesced runs.  No
+// inter-CTA spin-waits: tiles only communicate through the scanned histogram.
+#include "common.cuh"
+
+namespace {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_BLOCK = 512;
+constexpr int SORT_IPT = 16;
+constexpr int SORT_TILE = SORT_BLOCK * SORT_IPT;  // 8192 keys per CTA
+constexpr int SORT_NW = SORT_BLOCK / 32;
+
+// ---- statistics that fix the key layout ----------------------------------------------------------
+struct EventStats {
+  long long ts_min, ts_max;
+  unsigned long long n_live, n_unsupported;
+  unsigned int max_grp, bad;
+  unsigned int pad[2];
+};
+
+__global__ void k_ident_stats(const lsg_ident *__restrict__ idents, uint32_t n, EventStats *st) {
+  unsigned int m = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = max(m, idents[i].grp);
+  for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(&st->max_grp, m);
+}
+
+__device__ __forceinline__ bool event_live(const EventRec &e, const lsg_ident *idents, uint32_t n_idents, uint32_t *grp,
+                                           bool *bad) {
+  *grp = 0;
+  if (e.ident >= n_idents) { *bad = true; return false; }
+  if ((e.trace_sig & 15u) >= LSG_NSIG) return false;  // signalAttrKey: unsupported (correlator.go:73-77)
+  if (e.ts == LSG_TS_ZERO) return false;               // zero Time never matches (dns.go:108)
+  *grp = load_ident(idents, e.ident).grp;
+  return *grp != 0;
+}
+
+__global__ void __launch_bounds__(256)
+k_event_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+              EventStats *st) {
+  long long tmin = INT64_MAX, tmax = INT64_MIN;
+  unsigned int live = 0, unsup = 0;
+  bool bad = false;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    EventRec e = load_event(events + i);
+    uint32_t g;
+    if ((e.trace_sig & 15u) >= LSG_NSIG) unsup++;
+    if (event_live(e, idents, n_idents, &g, &bad)) {
+      live++;
+      tmin = min(tmin, (long long)e.ts);
+      tmax = max(tmax, (long long)e.ts);
+    }
+  }
+  for (int o = 16; o; o >>= 1) {
+    tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+    tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+    live += __shfl_xor_sync(0xffffffffu, live, o);
+    unsup += __shfl_xor_sync(0xffffffffu, unsup, o);
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&st->bad, 1u);
+  if ((threadIdx.x & 31) == 0) {
+    if (live) {
+      atomicMin(&st->ts_min, tmin);
+      atomicMax(&st->ts_max, tmax);
+      atomicAdd(&st->n_live, (unsigned long long)live);
+    }
+    if (unsup) atomicAdd(&st->n_unsupported, (unsigned long long)unsup);
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+k_event_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+             KeySpec ks, KeyT *__restrict__ keys) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    EventRec e = load_event(events + i);
+    uint32_t g;
+    bool bad = false;
+    KeyT k = (KeyT)~(KeyT)0;
+    if (event_live(e, idents, n_idents, &g, &bad)) k = (KeyT)lsg_make_key(ks, g, e.ts);
+    keys[i] = k;
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__restrict__ idents, KeySpec ks, int64_t ts_max,
+            KeyT *__restrict__ keys) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    SpanRec s = load_span(spans + i);
+    KeyT k = (KeyT)~(KeyT)0;
+    uint32_t g = load_ident(idents, s.ident).grp;   // ident range is validated by the join's caller
+    if (g != 0 && s.ts != LSG_TS_ZERO) {
+      int64_t t = s.ts < ks.ts_min ? ks.ts_min : (s.ts > ts_max ? ts_max : s.ts);   // processing order only
+      k = (KeyT)lsg_make_key(ks, g, t);
+    }
+    keys[i] = k;
+  }
+}
+
+// ---- one radix pass ------------------------------------------------------------------------------
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_BLOCK)
+k_radix_hist(const KeyT *__restrict__ keys, size_t n, int shift, uint32_t *__restrict__ tile_hist, uint32_t n_tiles) {
+  __shared__ uint32_t s_hist[RADIX];
+  for (int i = threadIdx.x; i < RADIX; i += SORT_BLOCK) s_hist[i] = 0;
+  __syncthreads();
+  const size_t base = (size_t)blockIdx.x * SORT_TILE;
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll 4
+  for (int i = 0; i < SORT_IPT; ++i) {
+    size_t pos = base + (size_t)i * SORT_BLOCK + threadIdx.x;
+    bool valid = pos < n;
+    unsigned d = valid ? (unsigned)((keys[pos] >> shift) & (RADIX - 1)) : 0xffffffffu;
+    unsigned m = __match_any_sync(0xffffffffu, d);
+    if (valid && lane == (unsigned)(__ffs(m) - 1)) atomicAdd(&s_hist[d], __popc(m));
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < RADIX; d += SORT_BLOCK) tile_hist[(size_t)d * n_tiles + blockIdx.x] = s_hist[d];
+}
+
+// exclusive scan of each digit's row over the tiles (in place); one CTA per digit
+__global__ void __launch_bounds__(1024)
+k_radix_scan_tiles(uint32_t *__restrict__ tile_hist, uint32_t n_tiles, uint32_t *__restrict__ digit_total) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_carry;
+  uint32_t *row = tile_hist + (size_t)blockIdx.x * n_tiles;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < n_tiles; base += 1024) {
+    uint32_t i = base + threadIdx.x;
+    uint32_t v = i < n_tiles ? row[i] : 0, x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t w = s_warp[lane], z = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t y = __shfl_up_sync(0xffffffffu, z, o);
+        if (lane >= (unsigned)o) z += y;
+      }
+      s_warp[lane] = z - w;  // exclusive over warps
+    }
+    __syncthreads();
+    uint32_t carry = s_carry;
+    if (i < n_tiles) row[i] = carry + s_warp[warp] + x - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = carry + s_warp[warp] + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) digit_total[blockIdx.x] = s_carry;
+}
+
+__global__ void __launch_bounds__(RADIX) k_radix_scan_digits(const uint32_t *__restrict__ digit_total, uint32_t *__restrict__ digit_base) {
+  __shared__ uint32_t s_warp[RADIX / 32];
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t v = digit_total[threadIdx.x], x = v;
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_warp[warp] = x;
+  __syncthreads();
+  uint32_t pre = 0;
+  for (unsigned w = 0; w < warp; ++w) pre += s_warp[w];
+  digit_base[threadIdx.x] = pre + x - v;
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_BLOCK)
+k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ idx_in, KeyT *__restrict__ keys_out,
+                uint32_t *__restrict__ idx_out, size_t n, int shift, const uint32_t *__restrict__ tile_off,
+                const uint32_t *__restrict__ digit_base, uint32_t n_tiles) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint32_t *warp_cnt = reinterpret_cast<uint32_t *>(smem);  // [SORT_NW][RADIX]
+  uint32_t *bin_off = warp_cnt + SORT_NW * RADIX;           // [RADIX] first tile-local slot of each digit
+  uint32_t *gbase = bin_off + RADIX;                        // [RADIX] global position of tile-local slot 0, per digit
+  uint32_t *s_scan = gbase + RADIX;                         // [8]
+  uint32_t *s_idx = s_scan + 8;                             // [SORT_TILE]
+  KeyT *s_keys = reinterpret_cast<KeyT *>(s_idx + SORT_TILE);  // [SORT_TILE]
+
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const size_t base = (size_t)blockIdx.x * SORT_TILE;
+  const uint32_t count = (uint32_t)min((size_t)SORT_TILE, n - base);
+  for (int i = tid; i < SORT_NW * RADIX; i += SORT_BLOCK) warp_cnt[i] = 0;
+  __syncthreads();
+
+  // warp-striped load: warp w owns tile slots [w*32*IPT, (w+1)*32*IPT), item i of lane l is slot i*32+l
+  KeyT k[SORT_IPT];
+  uint32_t v[SORT_IPT];
+  uint32_t rank[SORT_IPT];
+  const size_t wbase = base + (size_t)warp * 32 * SORT_IPT;
+#pragma unroll
+  for (int i = 0; i < SORT_IPT; ++i) {
+    size_t pos = wbase + (size_t)i * 32 + lane;
+    bool valid = pos < n;
+    k[i] = valid ? keys_in[pos] : (KeyT)~(KeyT)0;   // padding sorts behind every real key of the tile (stable)
+    v[i] = valid ? (idx_in ? idx_in[pos] : (uint32_t)pos) : 0u;
+  }
+  // stable rank of each item among the items of its warp with the same digit
+  uint32_t *my_cnt = warp_cnt + warp * RADIX;
+  const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int i = 0; i < SORT_IPT; ++i) {
+    unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
+    unsigned m = __match_any_sync(0xffffffffu, d);
+    int leader = __ffs(m) - 1;
+    uint32_t old = 0;
+    if ((int)lane == leader) {
+      old = my_cnt[d];
+      my_cnt[d] = old + __popc(m);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[i] = old + __popc(m & lt_mask);
+    __syncwarp();
+  }
+  __syncthreads();
+  // per digit: exclusive scan over the warps, then over the digits
+  uint32_t total = 0;
+  if (tid < RADIX) {
+    uint32_t run = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_NW; ++w) {
+      uint32_t c = warp_cnt[w * RADIX + tid];
+      warp_cnt[w * RADIX + tid] = run;
+      run += c;
+    }
+    total = run;
+  }
+  uint32_t x = total;
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (tid < RADIX && lane == 31) s_scan[warp] = x;
+  __syncthreads();
+  if (tid < RADIX) {
+    uint32_t pre = 0;
+    for (unsigned w = 0; w < warp; ++w) pre += s_scan[w];
+    uint32_t excl = pre + x - total;
+    bin_off[tid] = excl;
+    gbase[tid] = digit_base[tid] + tile_off[(size_t)tid * n_tiles + blockIdx.x] - excl;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < SORT_IPT; ++i) {
+    unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
+    uint32_t lp = bin_off[d] + my_cnt[d] + rank[i];
+    s_keys[lp] = k[i];
+    s_idx[lp] = v[i];
+  }
+  __syncthreads();
+  // tile is now in digit order in shared memory: runs of equal digits go to consecutive global slots
+  for (uint32_t j = tid; j < count; j += SORT_BLOCK) {
+    KeyT key = s_keys[j];
+    unsigned d = (unsigned)((key >> shift) & (RADIX - 1));
+    size_t out = (size_t)gbase[d] + j;
+    keys_out[out] = key;
+    idx_out[out] = s_idx[j];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n,
+                lsg_event *__restrict__ sorted) {
+  // two lanes per record: each moves one 16-byte half, so a warp writes 512 contiguous bytes
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; t < 2 * n; t += stride) {
+    size_t j = t >> 1;
+    unsigned half = (unsigned)(t & 1);
+    uint32_t src = perm[j];
+    uint4 val = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src) + half);
+    st_v4(reinterpret_cast<uint4 *>(sorted + j) + half, val);
+  }
+}
+
+size_t scatter_smem(size_t key_bytes) {
+  return (size_t)(SORT_NW * RADIX + RADIX + RADIX + 8 + SORT_TILE) * 4 + (size_t)SORT_TILE * key_bytes;
+}
+
+inline unsigned grid_for(lsg_ctx *ctx, size_t n, int block, int per_sm) {
+  size_t blocks = (n + block - 1) / block;
+  size_t cap = (size_t)ctx->sm_count * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  return (unsigned)blocks;
+}
+
+// LSD radix sort of (key, idx) pairs over key bits [0, bits).  Result pointers are returned (ping or pong).
+template <typename KeyT>
+int radix_sort_pairs(lsg_ctx *ctx, KeyT *keys_a, KeyT *keys_b, uint32_t *idx_a, uint32_t *idx_b, size_t n, int bits,
+                     int slot_hist, KeyT **keys_out, uint32_t **idx_out, int prof_base = -1) {
+  const uint32_t n_tiles = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
+  void *hist_v = nullptr;
+  LSG_TRY(lsg_ws(ctx, slot_hist, ((size_t)RADIX * n_tiles + 2 * RADIX) * 4, &hist_v));
+  uint32_t *tile_hist = (uint32_t *)hist_v;
+  uint32_t *digit_total = tile_hist + (size_t)RADIX * n_tiles;
+  uint32_t *digit_base = digit_total + RADIX;
+  const size_t smem = scatter_smem(sizeof(KeyT));
+  LSG_CUDA(ctx, cudaFuncSetAttribute(k_radix_scatter<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
+  KeyT *kin = keys_a, *kout = keys_b;
+  uint32_t *iin = nullptr, *iout = idx_b;  // first pass: identity indices
+  uint32_t *ia = idx_a, *ib = idx_b;
+  for (int p = 0; p < passes; ++p) {
+    const int shift = p * RADIX_BITS;
+    {
+      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_HIST);
+      k_radix_hist<KeyT><<<n_tiles, SORT_BLOCK, 0, ctx->stream>>>(kin, n, shift, tile_hist, n_tiles);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    {
+      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCAN);
+      k_radix_scan_tiles<<<RADIX, 1024, 0, ctx->stream>>>(tile_hist, n_tiles, digit_total);
+      LSG_LAUNCH_CHECK(ctx);
+      k_radix_scan_digits<<<1, RADIX, 0, ctx->stream>>>(digit_total, digit_base);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    iout = (p & 1) ? ia : ib;
+    {
+      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCATTER);
+      k_radix_scatter<KeyT><<<n_tiles, SORT_BLOCK, smem, ctx->stream>>>(kin, iin, kout, iout, n, shift, tile_hist, digit_base,
+                                                                     n_tiles);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    KeyT *t = kin; kin = kout; kout = t;
+    iin = iout;
+  }
+  *keys_out = kin;
+  *idx_out = iin;
+  return 0;
+}
+
+int bits_of(uint64_t v) {
+  int b = 0;
+  while (v) { b++; v >>= 1; }
+  return b;
+}
+
+}  // namespace
+
+// Sort events by (grp, quantised time).  Fills `out`; records land in `sorted_out` (or a workspace buffer if NULL).
+int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                    int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
+  memset(out, 0, sizeof *out);
+  out->n = n;
+  if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_events %zu does not fit 32-bit indices", n);
+  void *small_v = nullptr;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  EventStats *st_dev = (EventStats *)small_v;
+  EventStats init;
+  memset(&init, 0, sizeof init);
+  init.ts_min = INT64_MAX;
+  init.ts_max = INT64_MIN;
+  EventStats *pin = (EventStats *)ctx->pinned;
+  *pin = init;
+  LSG_CUDA(ctx, cudaMemcpyAsync(st_dev, pin, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  {
+  ProfScope ps_stats(ctx, PK_STATS);
+  if (n_idents) {
+    k_ident_stats<<<grid_for(ctx, n_idents, 256, 1), 256, 0, ctx->stream>>>(idents, (uint32_t)n_idents, st_dev);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  if (n) {
+    k_event_stats<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, st_dev);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  }
+  LSG_CUDA(ctx, cudaMemcpyAsync(pin, st_dev, sizeof init, cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  EventStats st = *pin;
+  if (st.bad) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
+  out->n_live = st.n_live;
+  out->n_unsupported = st.n_unsupported;
+  KeySpec ks;
+  ks.ts_min = st.n_live ? st.ts_min : 0;
+  const uint64_t range = st.n_live ? (uint64_t)st.ts_max - (uint64_t)st.ts_min : 0;
+  ks.shift = 0;
+  if (!exact) {
+    // largest quantum <= window/64: a span's scan range grows by at most 2 quanta (~3%)
+    while (ks.shift < 40 && ((int64_t)1 << (ks.shift + 1)) <= window_ns / 64) ks.shift++;
+  }
+  ks.tbits = (uint32_t)bits_of(range >> ks.shift);
+  if (ks.tbits == 0) ks.tbits = 1;
+  const int gbits = bits_of(st.max_grp);
+  ks.bits = ks.tbits + gbits;
+  if (ks.bits > 62)
+    return lsg_fail(ctx, LSG_ERR_RANGE, "sort key needs %u bits (time range %llu ns, %u groups): more than 62", ks.bits,
+                    (unsigned long long)range, st.max_grp);
+  out->key = ks;
+  if (n == 0) return 0;
+  const bool k32 = ks.bits <= 31;
+  void *ka, *kb, *ia, *ib;
+  LSG_TRY(lsg_ws(ctx, WS_KEYS_A, n * (k32 ? 4 : 8), &ka));
+  LSG_TRY(lsg_ws(ctx, WS_KEYS_B, n * (k32 ? 4 : 8), &kb));
+  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4, &ia));
+  LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4, &ib));
+  uint32_t *perm = nullptr;
+  // sort bits + 1 so that the all-ones key of dead records lands behind every live key
+  if (k32) {
+    {
+      ProfScope ps(ctx, PK_KEYS);
+      k_event_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint32_t *)ka);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    uint32_t *ko;
+    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    out->keys = ko;
+  } else {
+    {
+      ProfScope ps(ctx, PK_KEYS);
+      k_event_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint64_t *)ka);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    uint64_t *ko;
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    out->keys = ko;
+  }
+  out->perm = perm;
+  if (!sorted_out) {
+    void *sv;
+    LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n * sizeof(lsg_event), &sv));
+    sorted_out = (lsg_event *)sv;
+  }
+  {
+    ProfScope ps(ctx, PK_GATHER);
+    k_gather_events<<<grid_for(ctx, 2 * n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, sorted_out);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  out->rec = sorted_out;
+  return 0;
+}
+
+// Processing order of the spans: same key as the events, so consecutive spans read overlapping event ranges.
+int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &ks,
+                   const uint32_t **perm_out) {
+  *perm_out = nullptr;
+  if (n == 0) return 0;
+  if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_spans %zu does not fit 32-bit indices", n);
+  const bool k32 = ks.bits <= 31;
+  void *ka, *kb, *ia, *ib;
+  LSG_TRY(lsg_ws(ctx, WS_SPAN_KEYS_A, n * (k32 ? 4 : 8), &ka));
+  LSG_TRY(lsg_ws(ctx, WS_SPAN_KEYS_B, n * (k32 ? 4 : 8), &kb));
+  LSG_TRY(lsg_ws(ctx, WS_SPAN_IDX_A, n * 4, &ia));
+  LSG_TRY(lsg_ws(ctx, WS_SPAN_IDX_B, n * 4, &ib));
+  // ts_max of the key space: the largest quantised time representable
+  const int64_t ts_max = (int64_t)((uint64_t)ks.ts_min + ((((uint64_t)1 << ks.tbits) - 1) << ks.shift));
+  uint32_t *perm = nullptr;
+  ProfScope ps_span(ctx, PK_SPAN_SORT);
+  const bool saved_prof = ctx->prof;
+  ctx->prof = false;   // the passes of the span sort are accounted as one PK_SPAN_SORT interval
+  struct Restore { lsg_ctx *c; bool v; ~Restore() { c->prof = v; } } restore{ctx, saved_prof};
+  if (k32) {
+    k_span_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint32_t *)ka);
+    LSG_LAUNCH_CHECK(ctx);
+    uint32_t *ko;
+    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+  } else {
+    k_span_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint64_t *)ka);
+    LSG_LAUNCH_CHECK(ctx);
+    uint64_t *ko;
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+  }
+  *perm_out = perm;
+  return 0;
+}

@@ -1,0 +1,291 @@
+"""GPU parity, part 2: the CUDA path against the CPU oracle on seeded inputs through the C ABI —
+randomised string batches (via the interner), the synthetic workload at sizes the oracle finishes in
+seconds, edge cases, and size-independent properties at BASELINE.json's full C2 size.
+Bit-exact: match sets and their order, tiers, counters, per-signal max, retrieval sums, elevated masks,
+argmax labels, confusion counts.  Within 1e-6 relative: posteriors, feature sums."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+from llm_slo_ebpf_toolkit_b200 import _abi as A
+from llm_slo_ebpf_toolkit_b200 import ebpfcorrelator as EC
+from llm_slo_ebpf_toolkit_b200 import correlation as CO
+from llm_slo_ebpf_toolkit_b200 import synth
+from llm_slo_ebpf_toolkit_b200.interner import Interner
+from oracle import cpu as O
+from oracle import ref_str as R
+from tests.randgen import random_batch
+
+pytestmark = pytest.mark.gpu
+
+
+def _eq_batch(got, want, fanout=None):
+    for k in ("cand_event", "cand_tier", "conf", "retrieval", "n_cand"):
+        assert np.array_equal(got[k], want[k]), k
+    assert np.array_equal(np.nan_to_num(got["attr"], nan=-1e300), np.nan_to_num(want["attr"], nan=-1e300)), "attr"
+    assert got["debug"].as_tuple() == want["debug"].as_tuple()
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_string_batches_vs_string_oracle(ctx, seed):
+    spans, signals = random_batch(100 + seed, 40, 300, n_pods=3 + seed % 4, dense=seed % 2 == 0)
+    params = [(2000, 0.7, 3), (2000, 0.85, 1), (300, 0.7, 8), (50, 0.5, 3), (5000, 0.95, 2), (0, 0.0, 0), (2000, 0.6, 5),
+              (120, 0.9, 4)][seed]
+    want = R.Correlator(*params).ProcessBatch(spans, signals)
+    mine = EC.Correlator(params[0], params[1], params[2], ctx).ProcessBatch(
+        [EC.SpanRecord(s.TraceID, s.SpanID, s.Service, s.Node, s.Pod, s.PID, s.ConnTuple, s.Timestamp, s.Attributes)
+         for s in spans],
+        [CO.SignalRef(g.Signal, g.TraceID, g.Service, g.Node, g.Pod, g.PID, g.ConnTuple, g.Timestamp, g.Value) for g in signals])
+    assert (mine.Debug.Unmatched, mine.Debug.LowConfidence, mine.Debug.FanoutDropped, mine.Debug.UnsupportedType) == \
+        (want.Debug.Unmatched, want.Debug.LowConfidence, want.Debug.FanoutDropped, want.Debug.UnsupportedType)
+    for g, w in zip(mine.Spans, want.Spans):
+        assert g.Attributes == w.Attributes
+        assert [c.Index for c in g.Candidates] == [c.Index for c in w._candidates]
+        assert [c.Decision.Tier for c in g.Candidates] == [c.Decision.Tier for c in w._candidates]
+
+
+@pytest.mark.parametrize("window_ms,thr,fanout,horizon_s,n_pods,ppg", [
+    (2000, 0.7, 3, 36, 64, 2), (2000, 0.7, 3, 3600, 64, 2), (100, 0.85, 1, 36, 16, 1), (5000, 0.6, 8, 20, 8, 4),
+    (2000, 1.0, 2, 36, 64, 2), (250, 0.7, 5, 4, 4, 2),
+])
+def test_synthetic_vs_indexed_oracle(ctx, window_ms, thr, fanout, horizon_s, n_pods, ppg):
+    cfg = synth.config(200_000, 20_000, n_pods, max(ppg, 8 if n_pods >= 8 else n_pods), ppg, seed=window_ms + fanout,
+                       horizon_ns=horizon_s * 1_000_000_000, multi_fault=fanout % 2)
+    w = synth.generate_host(cfg)
+    got = ctx.process_batch(w["spans"], w["events"], w["idents"], window_ms * 1_000_000, thr, fanout)
+    want = O.process_batch(w["spans"], w["events"], w["idents"], window_ms * 1_000_000, thr, fanout, indexed=True, nthreads=8)
+    _eq_batch(got, want)
+    assert (got["cand_event"] != A.NONE).sum() > 1000
+
+
+def test_brute_force_subsample(ctx):
+    """the literal O(S x E) restatement of the reference loop on a sub-sample"""
+    cfg = synth.config(50_000, 2_000, 16, 8, 2, seed=5, horizon_ns=10_000_000_000)
+    w = synth.generate_host(cfg)
+    got = ctx.process_batch(w["spans"], w["events"], w["idents"])
+    want = O.process_batch(w["spans"], w["events"], w["idents"], indexed=False, nthreads=8)
+    _eq_batch(got, want)
+
+
+def test_edge_cases(ctx):
+    cfg = synth.config(3000, 300, 8, 4, 2, seed=9, horizon_ns=5_000_000_000)
+    w = synth.generate_host(cfg)
+    ev, sp, ids = w["events"].copy(), w["spans"].copy(), w["idents"].copy()
+    # empty sides
+    for e, s in ((ev[:0], sp), (ev, sp[:0]), (ev[:0], sp[:0])):
+        _eq_batch(ctx.process_batch(s, e, ids), O.process_batch(s, e, ids, indexed=True))
+    # zero times, group 0, all events unsupported, base attributes, a wide time range (64-bit keys)
+    ev2, sp2, ids2 = ev.copy(), sp.copy(), ids.copy()
+    ev2["ts_ns"][::7] = A.TS_ZERO
+    sp2["ts_ns"][::11] = A.TS_ZERO
+    ids2["grp"][3] = 0
+    base = np.full((len(sp2), A.NSIG), np.nan)
+    base[::3, 0] = 1e9
+    base[1::3, 3] = -5.0
+    _eq_batch(ctx.process_batch(sp2, ev2, ids2, attr_base=base), O.process_batch(sp2, ev2, ids2, attr_base=base, indexed=False))
+    ev3 = ev.copy()
+    ev3["trace_sig"] |= 15
+    _eq_batch(ctx.process_batch(sp, ev3, ids), O.process_batch(sp, ev3, ids, indexed=False))
+    ev4, sp4 = ev.copy(), sp.copy()
+    ev4["ts_ns"][::2] += 400 * 86400 * 10**9      # 400 days apart: > 2^53 ns, needs 64-bit keys
+    sp4["ts_ns"][::2] += 400 * 86400 * 10**9
+    ev4["ts_ns"][5] = -(1 << 62)
+    sp4["ts_ns"][7] = (1 << 62)
+    _eq_batch(ctx.process_batch(sp4, ev4, ids), O.process_batch(sp4, ev4, ids, indexed=False))
+    # one group, every timestamp equal: a single key
+    ev5, sp5 = ev.copy(), sp.copy()
+    ev5["ts_ns"][:] = 12345
+    sp5["ts_ns"][:] = 12345
+    ids5 = ids.copy()
+    ids5["grp"][:] = 1
+    _eq_batch(ctx.process_batch(sp5, ev5, ids5), O.process_batch(sp5, ev5, ids5, indexed=False))
+    # errors: ident out of range, oversized fanout / window
+    bad = ev.copy()
+    bad["ident"][10] = 9999
+    import llm_slo_ebpf_toolkit_b200 as pkg
+    with pytest.raises(pkg.LsgError) as e:
+        ctx.process_batch(sp, bad, ids)
+    assert e.value.code == -4
+    with pytest.raises(pkg.LsgError):
+        ctx.process_batch(sp, ev, ids, fanout=9)
+    with pytest.raises(pkg.LsgError):
+        ctx.process_batch(sp, ev, ids, window_ns=1 << 53)
+
+
+def test_match_pairs_vs_oracle(ctx):
+    cfg = synth.config(100_000, 100_000, 16, 8, 2, seed=3, horizon_ns=2_000_000_000)
+    w = synth.generate_host(cfg)
+    rng = np.random.default_rng(1)
+    em = rng.integers(0, 2, 100_000).astype(np.uint8)
+    et = rng.integers(0, 5, 100_000).astype(np.uint8)
+    for window, thr in ((0, 0.0), (300_000_000, 0.85), (50_000_000, 0.5), (5_000_000_000, 1.0)):
+        t1, p1, e1 = ctx.match_pairs(w["spans"], w["events"], w["idents"], window, thr, em, et)
+        t2, p2, e2 = O.match_pairs(w["spans"], w["events"], w["idents"], window, thr, em, et)
+        assert np.array_equal(t1, t2) and np.array_equal(p1, p2) and bytes(e1) == bytes(e2)
+    assert len(set(t2)) == 5
+
+
+def test_attribute_features_confusion_vs_oracle(ctx):
+    rng = np.random.default_rng(7)
+    n = 50_000
+    sig = rng.choice([np.nan, 0.0, 0.5, 1.0, 2.0, 5.0, 10.0, 39.999, 40.0, 60.0, 80.0, 250.0], size=(n, A.NSIG))
+    sig[::97] = np.nan
+    rule = rng.integers(0, 8, n).astype(np.uint8)
+    post, top1, elev = ctx.attribute(sig, None, rule)
+    opost, otop1, oelev = O.attribute(O.default_model(), sig, None, rule)
+    assert np.array_equal(top1, otop1) and np.array_equal(elev, oelev)
+    assert np.array_equal(np.isnan(post), np.isnan(opost))
+    ok = ~np.isnan(opost)
+    assert np.all(np.abs(post[ok] - opost[ok]) <= 1e-6 * opost[ok])     # north_star tolerance
+    assert np.max(np.abs(post[ok] - opost[ok]) / opost[ok]) < 1e-12    # in practice a few ulp
+    has = rng.integers(0, 2, n).astype(np.uint8)
+    a1, a2 = ctx.attribute(sig, has, rule), O.attribute(O.default_model(), sig, has, rule)
+    assert np.array_equal(a1[1], a2[1]) and np.array_equal(a1[2], a2[2])
+    # confusion
+    actual = rng.integers(0, 10, n).astype(np.uint8)
+    exp_n = rng.integers(1, 4, n).astype(np.uint8)
+    exp = rng.integers(0, 1 << 12, n).astype(np.uint32) & np.uint32(0x777)
+    exp[::5] |= 0xF
+    pred = np.where(top1 == 0xFF, 7, top1).astype(np.uint8)
+    for thr, floor in ((0.10, 0.01), (0.0, 0.0), (0.5, 0.01)):
+        c1 = ctx.confusion(actual, pred, exp, exp_n, post, thr, floor)
+        c2 = O.confusion(actual, pred, exp, exp_n, opost, thr, floor)
+        assert bytes(c1) == bytes(c2)
+    assert bytes(ctx.confusion(actual, pred, exp, exp_n, None, 0.1, 0.01)) == bytes(O.confusion(actual, pred, exp, exp_n, None, 0.1, 0.01))
+    # features
+    ns, ni = 120_000, 9_000
+    attr = rng.choice([np.nan, np.nan, -1.0, 0.0, 0.3, 7.0, 100.0, 5000.0], size=(ns, A.NSIG))
+    inc = np.sort(rng.integers(0, ni, ns)).astype(np.uint32)
+    inc[::13] = A.NONE
+    inc[5::1000] = rng.integers(0, ni, len(inc[5::1000]))
+    s1, f1 = ctx.incident_features(attr, inc, ni, want_features=True)
+    s2, f2 = O.incident_features(attr, inc, ni, want_features=True)
+    assert np.array_equal(np.nan_to_num(s1, nan=-1e300), np.nan_to_num(s2, nan=-1e300))
+    assert np.array_equal(f1["count"], f2["count"]) and np.array_equal(f1["sketch"], f2["sketch"])
+    assert np.allclose(f1["sum"], f2["sum"], rtol=1e-6, atol=1e-9)
+
+
+def _dev_setup(ctx, cfg, **kw):
+    from llm_slo_ebpf_toolkit_b200.device import DeviceWorkload
+    return DeviceWorkload(ctx, cfg, **kw)
+
+
+def test_device_generator_equals_host_generator(ctx):
+    for multi in (0, 1):
+        cfg = synth.config(100_000, 10_000, 32, 8, 2, seed=11, multi_fault=multi, rank=multi, world=2)
+        w = synth.generate_host(cfg)
+        d = _dev_setup(ctx, cfg)
+        assert d.host("events", A.EVENT_DTYPE).tobytes() == w["events"].tobytes()
+        assert d.host("spans", A.SPAN_DTYPE).tobytes() == w["spans"].tobytes()
+        assert d.host("idents", A.IDENT_DTYPE).tobytes() == w["idents"].tobytes()
+        assert np.array_equal(d.host("inc_actual", np.uint8)[: len(w["inc_actual"])], w["inc_actual"])
+        assert np.array_equal(d.host("inc_expected", np.uint32)[: len(w["inc_actual"])], w["inc_expected"])
+
+
+def test_sort_events_exact(ctx):
+    import torch
+    cfg = synth.config(300_000, 1_000, 32, 8, 2, seed=13)
+    w = synth.generate_host(cfg)
+    ev = w["events"].copy()
+    ev["ts_ns"][::50] = ev["ts_ns"][1::50][: len(ev["ts_ns"][::50])]   # duplicate timestamps: stability is visible
+    ev["ts_ns"][::301] = A.TS_ZERO
+    d = _dev_setup(ctx, cfg, generate=False)
+    w2 = dict(w)
+    w2["events"] = ev
+    d.upload(w2)
+    n = len(ev)
+    out = torch.empty(n * 32, dtype=torch.uint8, device="cuda")
+    perm = torch.empty(n, dtype=torch.int32, device="cuda")
+    keys = torch.empty(n, dtype=torch.int64, device="cuda")
+    ctx.call_dev("lsg_sort_events_dev", d.events.data_ptr(), n, d.idents.data_ptr(), d.n_idents, out.data_ptr(),
+                 perm.data_ptr(), keys.data_ptr())
+    perm = perm.cpu().numpy().view(np.uint32)
+    keys = keys.cpu().numpy().view(np.uint64)
+    rec = out.cpu().numpy().view(A.EVENT_DTYPE)
+    assert np.array_equal(np.sort(perm), np.arange(n, dtype=np.uint32))           # a permutation
+    assert rec.tobytes() == ev[perm].tobytes()                                     # records follow it
+    assert np.all(keys[:-1] <= keys[1:])                                           # sorted
+    same = keys[:-1] == keys[1:]
+    assert np.all(perm[:-1][same] < perm[1:][same])                                # stable
+    grp = w["idents"]["grp"][ev["ident"]]
+    live = ((ev["trace_sig"] & 15) < A.NSIG) & (ev["ts_ns"] != A.TS_ZERO) & (grp != 0)
+    n_live = int(live.sum())
+    assert live[perm[:n_live]].all() and not live[perm[n_live:]].any()             # dead records sort last
+    order = np.lexsort((np.arange(n), ev["ts_ns"], grp))
+    assert np.array_equal(perm[:n_live], order[live[order]])                       # = stable sort by (grp, ts)
+
+
+def _oracle_pipeline(w, window_ns=0, thr=0.0, fanout=3, cov=0.10):
+    j = O.process_batch(w["spans"], w["events"], w["idents"], window_ns, thr, fanout, indexed=True, nthreads=8)
+    ni = len(w["inc_actual"])
+    sig = O.incident_features(j["attr"], w["spans"]["incident"], ni)
+    post, top1, elev = O.attribute(O.default_model(), sig)
+    conf = O.confusion(w["inc_actual"], top1, w["inc_expected"], w["inc_expected_n"], post, cov, 0.01)
+    return j, sig, post, top1, conf
+
+
+@pytest.mark.parametrize("multi", [0, 1])
+def test_pipeline_dev_vs_oracle(ctx, multi):
+    import torch
+    cfg = synth.config(1_000_000, 100_000, 64, 8, 2, seed=42, multi_fault=multi, horizon_ns=360_000_000_000)
+    w = synth.generate_host(cfg)
+    d = _dev_setup(ctx, cfg)
+    d.step()
+    d.step()        # a second pass over the same buffers gives the same result
+    torch.cuda.synchronize()
+    j, sig, post, top1, conf = _oracle_pipeline(w)
+    ns, ni = d.n_spans, d.n_incidents
+    assert np.array_equal(d.host("cand_event", np.uint32, (ns, 3)), j["cand_event"])
+    assert np.array_equal(d.host("cand_tier", np.uint8)[: ns * 3].reshape(ns, 3), j["cand_tier"])
+    assert np.array_equal(np.nan_to_num(d.host("attr", np.float64, (ns, A.NSIG)), nan=-1e300), np.nan_to_num(j["attr"], nan=-1e300))
+    assert np.array_equal(d.host("conf", np.float64)[:ns], j["conf"])
+    assert np.array_equal(np.nan_to_num(d.host("inc_signals", np.float64, (ni, A.NSIG)), nan=-1e300), np.nan_to_num(sig, nan=-1e300))
+    assert np.array_equal(d.host("top1", np.uint8)[:ni], top1)
+    gp = d.host("posterior", np.float64, (ni, A.NDOM))
+    ok = ~np.isnan(post)
+    assert np.array_equal(np.isnan(gp), np.isnan(post)) and np.all(np.abs(gp[ok] - post[ok]) <= 1e-6 * post[ok])
+    c = d.read_counters()
+    assert bytes(c.confusion) == bytes(conf)
+    assert c.debug.as_tuple() == j["debug"].as_tuple()
+    assert (c.events, c.spans, c.incidents) == (cfg.n_events, cfg.n_spans, ni)
+    assert c.candidates == int(j["n_cand"].sum()) and c.kept == int((j["cand_event"] != A.NONE).sum())
+
+
+def test_full_c2_properties(ctx):
+    """BASELINE.json configs[1] at full size (10 M events x 1 M spans): invariants that do not need the
+    brute force, plus exact comparison of sampled spans against the oracle on their own join group."""
+    import torch
+    cfg = synth.c2()
+    d = _dev_setup(ctx, cfg)
+    d.step()
+    torch.cuda.synchronize()
+    c = d.read_counters()
+    ns, ni = d.n_spans, d.n_incidents
+    m = np.array(c.confusion.matrix)
+    assert m.sum() + 0 == c.confusion.n == ni                                   # every incident lands in one cell
+    assert c.confusion.correct == np.trace(m[:8]) and c.confusion.partial >= c.confusion.correct
+    assert np.array(c.confusion.coverage).sum() == ni
+    cand = d.host("cand_event", np.uint32, (ns, 3))
+    tier = d.host("cand_tier", np.uint8)[: ns * 3].reshape(ns, 3)
+    kept = cand != A.NONE
+    assert c.kept == kept.sum() and c.candidates >= c.kept and c.debug.fanout_dropped == c.candidates - c.kept
+    assert np.all(kept[:, :-1] >= kept[:, 1:])                                  # kept candidates are a prefix
+    assert np.all((tier[:, :-1] <= tier[:, 1:]) | ~kept[:, 1:])                 # confidence never increases along it
+    ev = d.host("events", A.EVENT_DTYPE)
+    unsup = int(((ev["trace_sig"] & 15) >= A.NSIG).sum())
+    assert c.debug.unsupported_type == unsup * ns
+    assert c.debug.unmatched + c.debug.low_confidence + c.candidates == (cfg.n_events - unsup) * ns
+    # sampled join groups, exact
+    sp, ids = d.host("spans", A.SPAN_DTYPE), d.host("idents", A.IDENT_DTYPE)
+    attr = d.host("attr", np.float64, (ns, A.NSIG))
+    for g in (1, 17, 32):
+        smask = ids["grp"][sp["ident"]] == g
+        emask = ids["grp"][ev["ident"]] == g
+        sidx, eidx = np.nonzero(smask)[0][:4000], np.nonzero(emask)[0]
+        want = O.process_batch(sp[sidx], ev[eidx], ids, indexed=True, nthreads=8)
+        wc = np.where(want["cand_event"] == A.NONE, A.NONE, eidx[np.minimum(want["cand_event"], len(eidx) - 1)]).astype(np.uint32)
+        assert np.array_equal(cand[sidx], wc)
+        assert np.array_equal(tier[sidx], want["cand_tier"])
+        assert np.array_equal(np.nan_to_num(attr[sidx], nan=-1e300), np.nan_to_num(want["attr"], nan=-1e300))
