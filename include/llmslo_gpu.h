@@ -268,6 +268,8 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *args, lsg_counters *coun
 /* ---- per-kernel timing with CUDA events on the context's stream (bench.py's roofline numbers) ---------
  *  lsg_profile_read synchronises the stream, adds the finished intervals to per-kernel totals and copies
  *  up to `cap` of them out (milliseconds, launches-groups counted); returns the number of kinds. */
+/* key layout of the most recent event sort: total key bits, log2 of the time quantum in ns, radix passes */
+int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_shift, uint32_t *passes);
 int lsg_profile_enable(lsg_ctx *ctx, int on);
 const char *lsg_profile_name(int kind);
 int lsg_profile_read(lsg_ctx *ctx, double *ms, uint64_t *count, int cap, int reset);

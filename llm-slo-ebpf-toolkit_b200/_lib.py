@@ -72,6 +72,7 @@ def load_library():
         lib.lsg_synth_dev.argtypes = [vp, P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
         lib.lsg_synth_host.argtypes = [P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
         lib.lsg_pipeline.argtypes = [vp, P(A.PipelineArgs), P(A.Counters)]
+        lib.lsg_last_sort_info.argtypes = [vp, P(C.c_uint32), P(C.c_uint32), P(C.c_uint32)]
         lib.lsg_profile_enable.argtypes = [vp, cint]
         lib.lsg_profile_name.argtypes = [cint]
         lib.lsg_profile_name.restype = C.c_char_p
@@ -199,6 +200,11 @@ class Context:
                                             _ptr(posterior), float(coverage_thr), float(hyp_floor), len(actual),
                                             C.byref(out)))
         return out
+
+    def last_sort_info(self):
+        b, sh, ps = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._check(self._lib.lsg_last_sort_info(self._h, C.byref(b), C.byref(sh), C.byref(ps)))
+        return {"key_bits": b.value, "time_shift": sh.value, "passes": ps.value}
 
     def profile_enable(self, on=True):
         self._check(self._lib.lsg_profile_enable(self._h, 1 if on else 0))

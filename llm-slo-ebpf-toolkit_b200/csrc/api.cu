@@ -156,7 +156,7 @@ __global__ void k_finalize_counters(const unsigned long long *__restrict__ jc, u
 
 __global__ void k_widen_keys(const uint32_t *__restrict__ in, size_t n, unsigned long long *__restrict__ out) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    out[i] = in[i] == 0xffffffffu ? ~0ull : (unsigned long long)in[i];
+    out[i] = (unsigned long long)in[i];
 }
 
 }  // namespace
@@ -257,6 +257,14 @@ int lsg_profile_read(lsg_ctx *ctx, double *ms, uint64_t *count, int cap, int res
   if (reset)
     for (int i = 0; i < PK_COUNT; ++i) { ctx->prof_ms[i] = 0; ctx->prof_n[i] = 0; }
   return PK_COUNT;
+}
+
+int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_shift, uint32_t *passes) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if (key_bits) *key_bits = ctx->last_key.bits;
+  if (time_shift) *time_shift = ctx->last_key.shift;
+  if (passes) *passes = (ctx->last_key.bits + 7) / 8;
+  return 0;
 }
 
 const char *lsg_last_error(const lsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }

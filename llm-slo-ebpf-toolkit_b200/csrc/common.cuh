@@ -53,6 +53,18 @@ struct DevModel {
   uint32_t sig_mask;
 };
 
+// ---- sort key: (join group, quantised time) ------------------------------------------------------
+// live key = (grp << tbits) | ((ts - ts_min) >> shift); records that can match nothing (group 0, zero
+// Time, unsupported signal type) get the key (max_grp + 1) << tbits and sort behind everything a span
+// ever searches.
+struct KeySpec {
+  int64_t ts_min;
+  uint32_t shift;   // time quantum = 2^shift ns
+  uint32_t tbits;   // bits of the quantised time
+  uint32_t bits;    // total key bits (gbits + tbits)
+  uint64_t dead;    // key of records that can match nothing: one group past the last real one, so they sort last
+};
+
 // per-kernel timing (bench.py's roofline): CUDA events recorded on the context's stream around each launch
 enum {
   PK_STATS = 0, PK_KEYS, PK_HIST, PK_SCAN, PK_SCATTER, PK_GATHER, PK_SPAN_SORT, PK_JOIN, PK_FEATURES, PK_ATTRIBUTE,
@@ -78,6 +90,7 @@ struct lsg_ctx {
   size_t pinned_cap = 0;
   DevModel model;
   bool model_set = false;
+  KeySpec last_key = {};   // key layout of the most recent event sort (diagnostics)
 };
 
 int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...);
@@ -185,18 +198,10 @@ __device__ __forceinline__ lsg_ident load_ident(const lsg_ident *t, uint32_t row
 }
 #endif
 
-// ---- sort key: (join group, quantised time) ------------------------------------------------------
-// live key = (grp << tbits) | ((ts - ts_min) >> shift); records that can match nothing (group 0, zero
-// Time, unsupported signal type) get the all-ones key and sort behind everything a span ever searches.
-struct KeySpec {
-  int64_t ts_min;
-  uint32_t shift;   // time quantum = 2^shift ns
-  uint32_t tbits;   // bits of the quantised time
-  uint32_t bits;    // total key bits (gbits + tbits)
-};
 LSG_HD uint64_t lsg_make_key(const KeySpec &k, uint32_t grp, int64_t ts) {
   return ((uint64_t)grp << k.tbits) | (((uint64_t)ts - (uint64_t)k.ts_min) >> k.shift);
 }
+
 
 // stage kernels (defined across the .cu files)
 int lsg_launch_match_pairs(lsg_ctx *, const lsg_span *, const lsg_event *, size_t, const lsg_ident *, size_t, int64_t, double,

@@ -93,7 +93,7 @@ k_event_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
     EventRec e = load_event(events + i);
     uint32_t g;
     bool bad = false;
-    KeyT k = (KeyT)~(KeyT)0;
+    KeyT k = (KeyT)ks.dead;
     if (event_live(e, idents, n_idents, &g, &bad)) k = (KeyT)lsg_make_key(ks, g, e.ts);
     keys[i] = k;
   }
@@ -105,7 +105,7 @@ k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__res
             KeyT *__restrict__ keys) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     SpanRec s = load_span(spans + i);
-    KeyT k = (KeyT)~(KeyT)0;
+    KeyT k = (KeyT)ks.dead;
     uint32_t g = load_ident(idents, s.ident).grp;   // ident range is validated by the join's caller
     if (g != 0 && s.ts != LSG_TS_ZERO) {
       int64_t t = s.ts < ks.ts_min ? ks.ts_min : (s.ts > ts_max ? ts_max : s.ts);   // processing order only
@@ -404,12 +404,14 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
   }
   ks.tbits = (uint32_t)bits_of(range >> ks.shift);
   if (ks.tbits == 0) ks.tbits = 1;
-  const int gbits = bits_of(st.max_grp);
+  const int gbits = bits_of((uint64_t)st.max_grp + 1);   // one extra group id for the dead records
   ks.bits = ks.tbits + gbits;
+  ks.dead = ((uint64_t)st.max_grp + 1) << ks.tbits;
   if (ks.bits > 62)
     return lsg_fail(ctx, LSG_ERR_RANGE, "sort key needs %u bits (time range %llu ns, %u groups): more than 62", ks.bits,
                     (unsigned long long)range, st.max_grp);
   out->key = ks;
+  ctx->last_key = ks;
   if (n == 0) return 0;
   const bool k32 = ks.bits <= 31;
   void *ka, *kb, *ia, *ib;
@@ -418,7 +420,6 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
   LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4, &ia));
   LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4, &ib));
   uint32_t *perm = nullptr;
-  // sort bits + 1 so that the all-ones key of dead records lands behind every live key
   if (k32) {
     {
       ProfScope ps(ctx, PK_KEYS);
@@ -426,7 +427,7 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
       LSG_LAUNCH_CHECK(ctx);
     }
     uint32_t *ko;
-    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
     out->keys = ko;
   } else {
     {
@@ -435,7 +436,7 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
       LSG_LAUNCH_CHECK(ctx);
     }
     uint64_t *ko;
-    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
     out->keys = ko;
   }
   out->perm = perm;
@@ -476,12 +477,12 @@ int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_iden
     k_span_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint32_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint32_t *ko;
-    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
   } else {
     k_span_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint64_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint64_t *ko;
-    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits + 1, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
   }
   *perm_out = perm;
   return 0;

@@ -84,6 +84,9 @@ def test_edge_cases(ctx):
     base = np.full((len(sp2), A.NSIG), np.nan)
     base[::3, 0] = 1e9
     base[1::3, 3] = -5.0
+    # (group 0 is the contract's "matches nothing": only the group-aware indexed oracle models it)
+    _eq_batch(ctx.process_batch(sp2, ev2, ids2, attr_base=base), O.process_batch(sp2, ev2, ids2, attr_base=base, indexed=True))
+    ids2["grp"][3] = ids["grp"][3]
     _eq_batch(ctx.process_batch(sp2, ev2, ids2, attr_base=base), O.process_batch(sp2, ev2, ids2, attr_base=base, indexed=False))
     ev3 = ev.copy()
     ev3["trace_sig"] |= 15
