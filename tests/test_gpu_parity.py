@@ -118,16 +118,29 @@ def test_edge_cases(ctx):
 
 
 def test_match_pairs_vs_oracle(ctx):
-    cfg = synth.config(100_000, 100_000, 16, 8, 2, seed=3, horizon_ns=2_000_000_000)
+    cfg = synth.config(100_000, 20_000, 16, 8, 2, seed=3, horizon_ns=40_000_000_000)
     w = synth.generate_host(cfg)
+    ev, sp, ids = w["events"], w["spans"], w["idents"]
+    # pair every event with a plausible span: the owner of its trace id, else the span of its join group nearest in time
+    partner = np.zeros(len(ev), np.int64)
+    sgrp, egrp = ids["grp"][sp["ident"]], ids["grp"][ev["ident"]]
+    for g in np.unique(egrp):
+        sidx = np.nonzero(sgrp == g)[0]
+        sidx = sidx[np.argsort(sp["ts_ns"][sidx], kind="stable")]
+        eidx = np.nonzero(egrp == g)[0]
+        pos = np.clip(np.searchsorted(sp["ts_ns"][sidx], ev["ts_ns"][eidx]), 0, len(sidx) - 1)
+        partner[eidx] = sidx[pos]
+    tr = ev["trace_sig"] >> 4
+    partner[tr != 0] = tr[tr != 0].astype(np.int64) - 1
+    spans = sp[partner]
     rng = np.random.default_rng(1)
-    em = rng.integers(0, 2, 100_000).astype(np.uint8)
-    et = rng.integers(0, 5, 100_000).astype(np.uint8)
+    em = rng.integers(0, 2, len(ev)).astype(np.uint8)
+    et = rng.integers(0, 5, len(ev)).astype(np.uint8)
     for window, thr in ((0, 0.0), (300_000_000, 0.85), (50_000_000, 0.5), (5_000_000_000, 1.0)):
-        t1, p1, e1 = ctx.match_pairs(w["spans"], w["events"], w["idents"], window, thr, em, et)
-        t2, p2, e2 = O.match_pairs(w["spans"], w["events"], w["idents"], window, thr, em, et)
+        t1, p1, e1 = ctx.match_pairs(spans, ev, ids, window, thr, em, et)
+        t2, p2, e2 = O.match_pairs(spans, ev, ids, window, thr, em, et)
         assert np.array_equal(t1, t2) and np.array_equal(p1, p2) and bytes(e1) == bytes(e2)
-    assert len(set(t2)) == 5
+    assert sorted(set(t2)) == [0, 1, 2, 3, 4] and min(e2.matched_by_tier) > 50
 
 
 def test_attribute_features_confusion_vs_oracle(ctx):
