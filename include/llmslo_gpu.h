@@ -201,6 +201,26 @@ int lsg_incident_features(lsg_ctx *ctx, const double *span_attr, const uint32_t 
 int lsg_incident_features_dev(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
                               size_t n_incidents, double *signals_out, lsg_feature *features_out);
 
+/* No counterpart in the reference.  The same per-incident maxima as lsg_incident_features_dev (signals only, no
+ * count/sum/sketch), for callers that must not allocate device memory: a process whose whole GPU memory budget
+ * already belongs to its own pool, or a service that cannot take the device-wide synchronisation cudaMalloc and
+ * cudaFree imply while other streams are running.  It needs no lsg_ctx and calls no cudaMalloc, cudaFree or other
+ * allocating routine: the accumulators are a fixed array inside the library image (LSG_STATIC_MAX_INCIDENTS x 12
+ * x 8 bytes = 1.5 MiB of device memory on every GPU that loads the library, held until the process exits).
+ *   - all pointers are DEVICE pointers on the CURRENT device; `stream` is a cudaStream_t of that device (NULL = the
+ *     default stream).  The work is enqueued on `stream` and the call returns without synchronising.
+ *   - n_incidents > LSG_STATIC_MAX_INCIDENTS is refused with LSG_ERR_RANGE; split the batch or use the
+ *     allocating entry point.
+ *   - the first call on each device looks up the array's address on that device; make that first call before
+ *     starting any stream capture.
+ *   - every call on a device shares the one array and begins by clearing the part it uses, so the previous call's
+ *     values never leak in, but two calls whose work overlaps on the same GPU (different streams or threads)
+ *     race on it: keep calls on one device stream-ordered.
+ *   - errbuf (optional, errbuf_len bytes) receives a message when the return value is not 0. */
+#define LSG_STATIC_MAX_INCIDENTS 16384
+int lsg_incident_signals_static(void *stream, const double *span_attr, const uint32_t *span_incident, size_t n_spans,
+                                size_t n_incidents, double *signals_out, char *errbuf, size_t errbuf_len);
+
 /* ---- A9-A10: BayesianAttributor.Attribute (bayesian.go:218-284) and the numeric part of
  *      AttributeSample (bayesian.go:315-343) for a batch of incidents.
  *  signals     [n*12] FaultSample.Signals by signal index, NaN = key absent

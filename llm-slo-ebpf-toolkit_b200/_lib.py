@@ -77,6 +77,7 @@ def load_library():
         lib.lsg_profile_name.argtypes = [cint]
         lib.lsg_profile_name.restype = C.c_char_p
         lib.lsg_profile_read.argtypes = [vp, P(C.c_double), P(C.c_uint64), cint, cint]
+        lib.lsg_incident_signals_static.argtypes = [vp, vp, vp, sz, sz, vp, C.c_char_p, sz]
         lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
         lib.lsg_abi_sizes.restype = cint
         _LIB = lib

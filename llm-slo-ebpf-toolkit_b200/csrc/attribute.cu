@@ -1,6 +1,8 @@
 // attribute.cu — K-features (A7 glue), K-bayes (pkg/attribution/bayesian.go:218-284, 315-343) and
 // K-confusion (pkg/attribution/pipeline.go:65-185).
 #include <cmath>
+#include <cstdarg>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -249,5 +251,101 @@ int lsg_launch_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *pre
   k_confusion<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(actual, predicted, expected, expected_n, posterior,
                                                                   coverage_thr, hyp_floor, n, (unsigned long long *)out_dev);
   LSG_LAUNCH_CHECK(ctx);
+  return 0;
+}
+
+// ---- per-incident signal reduction without any allocation ---------------------------------------------
+//
+// lsg_incident_features[_dev] above keep their accumulators in a context workspace that is cudaMalloc'ed
+// on first use and whenever a batch outgrows it.  Some hosts cannot do that: a process that has already
+// handed the device's whole memory budget to its own pool has nothing left for cudaMalloc to give, and a
+// service that keeps other streams busy cannot afford cudaMalloc/cudaFree, which synchronise the whole
+// device.  For them the accumulators below live in the library image itself: a fixed array in device
+// global memory, present on every GPU that loads the library from load until exit
+// (LSG_STATIC_MAX_INCIDENTS x 12 x 8 bytes = 1.5 MiB per GPU), so the entry point never allocates.
+static __device__ __align__(256) unsigned long long g_static_incident_keys[(size_t)LSG_STATIC_MAX_INCIDENTS * LSG_NSIG];
+
+namespace {
+// In host code `g_static_incident_keys` is only a handle for the runtime, not an address a kernel could
+// use; the device address differs per GPU and is looked up once per device with that device current.
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned long long *g_static_keys_dev[kStaticMaxDevices] = {};
+int g_static_sm_count[kStaticMaxDevices] = {};
+
+void static_err(char *buf, size_t len, const char *fmt, ...) {
+  if (!buf || len == 0) return;
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, len, fmt, ap);
+  va_end(ap);
+}
+}  // namespace
+
+extern "C" int lsg_incident_signals_static(void *stream, const double *span_attr, const uint32_t *span_incident,
+                                           size_t n_spans, size_t n_incidents, double *signals_out, char *errbuf,
+                                           size_t errbuf_len) {
+  if (errbuf && errbuf_len) errbuf[0] = 0;
+  if ((n_spans && (!span_attr || !span_incident)) || (n_incidents && !signals_out)) {
+    static_err(errbuf, errbuf_len, "null argument");
+    return LSG_ERR_INVALID;
+  }
+  if (n_incidents > (size_t)LSG_STATIC_MAX_INCIDENTS) {
+    static_err(errbuf, errbuf_len, "n_incidents %zu exceeds LSG_STATIC_MAX_INCIDENTS (%d): the built-in scratch array "
+               "cannot hold this batch; split it or use lsg_incident_features_dev", n_incidents, LSG_STATIC_MAX_INCIDENTS);
+    return LSG_ERR_RANGE;
+  }
+  if (n_incidents == 0) return 0;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) {
+    static_err(errbuf, errbuf_len, "no current CUDA device (cudaGetDevice: %s)", cudaGetErrorString(e));
+    return e == cudaSuccess ? LSG_ERR_INVALID : LSG_ERR_NODEVICE;
+  }
+  unsigned long long *keys = nullptr;
+  int sms = 0;
+  {
+    // set-up, once per device, with that device current: resolve the array's address on this GPU
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_keys_dev[dev]) {
+      unsigned long long *p = nullptr;
+      e = cudaGetSymbolAddress((void **)&p, g_static_incident_keys);
+      if (e != cudaSuccess || !p) {
+        static_err(errbuf, errbuf_len, "cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        return LSG_ERR_CUDA;
+      }
+      int n_sm = 0;
+      e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+      if (e != cudaSuccess || n_sm <= 0) {
+        static_err(errbuf, errbuf_len, "cudaDeviceGetAttribute failed on device %d: %s", dev, cudaGetErrorString(e));
+        return LSG_ERR_CUDA;
+      }
+      g_static_sm_count[dev] = n_sm;
+      g_static_keys_dev[dev] = p;
+    }
+    keys = g_static_keys_dev[dev];
+    sms = g_static_sm_count[dev];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t n = n_incidents * LSG_NSIG;
+  // the array still holds the previous call's maxima: everything this call will read starts from "absent"
+  e = cudaMemsetAsync(keys, 0, n * sizeof(unsigned long long), st);
+  if (e != cudaSuccess) {
+    static_err(errbuf, errbuf_len, "cudaMemsetAsync failed: %s", cudaGetErrorString(e));
+    return LSG_ERR_CUDA;
+  }
+  auto blocks_for = [&](size_t items) {
+    size_t b = (items + 255) / 256, cap = (size_t)sms * 8;
+    return (unsigned)(b > cap ? cap : (b ? b : 1));
+  };
+  if (n_spans)
+    k_incident_accumulate<<<blocks_for(n_spans * LSG_NSIG), 256, 0, st>>>(span_attr, span_incident, nullptr, n_spans,
+                                                                        n_incidents, keys, nullptr);
+  k_incident_finish<<<blocks_for(n), 256, 0, st>>>(keys, n, signals_out);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    static_err(errbuf, errbuf_len, "kernel launch failed: %s", cudaGetErrorString(e));
+    return LSG_ERR_CUDA;
+  }
   return 0;
 }
