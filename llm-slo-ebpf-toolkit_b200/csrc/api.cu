@@ -112,7 +112,8 @@ int norm_params(lsg_ctx *ctx, int64_t *window_ns, double *threshold, int *fanout
 int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
                        const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
-                       double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted) {
+                       double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
+                       unsigned long long *inc_keys = nullptr, size_t n_incidents = 0) {
   LSG_TRY(lsg_sort_events(ctx, events, n_events, idents, n_idents, window_ns, false, nullptr, sorted));
   const uint32_t *span_perm = nullptr;
   LSG_TRY(lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm));
@@ -125,6 +126,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   ja.attr_base = attr_base; ja.cand_event = cand_event; ja.cand_tier = cand_tier; ja.attr_out = attr_out;
   ja.conf_out = conf_out; ja.retrieval_out = retrieval_out; ja.n_cand_out = n_cand_out;
   ja.counters = (uint64_t *)((char *)small_v + SMALL_JOIN);
+  ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
   LSG_TRY(lsg_launch_join(ctx, ja));
   *join_counters_dev = ja.counters;
   return 0;
@@ -540,10 +542,14 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   LSG_CUDA(ctx, cudaMemsetAsync(a->counters_dev, 0, sizeof(lsg_counters), ctx->stream));
   uint64_t *jc_dev = nullptr;
   SortedEvents sorted;
+  // the per-incident maxima (A7) are accumulated by the join's epilogue: no second pass over the span attributes
+  void *acc = nullptr;
+  LSG_TRY(lsg_ws(ctx, WS_FEAT, a->n_incidents * LSG_NSIG * 8, &acc));
+  LSG_CUDA(ctx, cudaMemsetAsync(acc, 0, a->n_incidents * LSG_NSIG * 8, ctx->stream));
   LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, a->events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
                              fanout, nullptr, a->cand_event, a->cand_tier, a->attr_out, a->conf_out, nullptr, nullptr, &jc_dev,
-                             &sorted));
-  LSG_TRY(lsg_launch_incident_features(ctx, a->attr_out, nullptr, a->spans, a->n_spans, a->n_incidents, a->inc_signals, nullptr));
+                             &sorted, (unsigned long long *)acc, a->n_incidents));
+  LSG_TRY(lsg_launch_incident_finish(ctx, (const unsigned long long *)acc, a->n_incidents, a->inc_signals));
   LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
   LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
                                0.01, a->n_incidents, a->counters_dev + 4));

@@ -11,17 +11,7 @@ namespace {
 // ---- K-features ------------------------------------------------------------------------------------
 // Per incident and signal: max over the incident's spans of the spans' enriched attribute (the only
 // aggregate the reference defines: correlator.go:109-111), plus count / sum / log2 sketch.
-// doubles are mapped to order-preserving unsigned keys so that max is an integer atomicMax;
-// key 0 is never produced by a non-NaN value and stands for "absent".
-__device__ __forceinline__ unsigned long long f64_key(double v) {
-  unsigned long long b = (unsigned long long)__double_as_longlong(v);
-  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
-}
-__device__ __forceinline__ double key_f64(unsigned long long k) {
-  if (k == 0) return __longlong_as_double(0x7ff8000000000000ll);
-  unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
-  return __longlong_as_double((long long)b);
-}
+// doubles are mapped to order-preserving unsigned keys (f64_key, common.cuh) so that max is an integer atomicMax.
 
 // one thread per (span, signal) element of the [n_spans][12] attribute matrix: coalesced 8-byte loads.
 // Lanes of a warp that hit the same (incident, signal) are combined by shuffles first (segmented
@@ -213,6 +203,15 @@ inline unsigned grid_for(lsg_ctx *ctx, size_t n, int block, int per_sm) {
 }
 
 }  // namespace
+
+int lsg_launch_incident_finish(lsg_ctx *ctx, const unsigned long long *keys, size_t n_incidents, double *signals_out) {
+  const size_t n = n_incidents * LSG_NSIG;
+  if (n == 0) return 0;
+  ProfScope ps(ctx, PK_FEATURES);
+  k_incident_finish<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(keys, n, signals_out);
+  LSG_LAUNCH_CHECK(ctx);
+  return 0;
+}
 
 int lsg_launch_incident_features(lsg_ctx *ctx, const double *span_attr, const uint32_t *span_incident, const lsg_span *spans,
                                  size_t n_spans, size_t n_incidents, double *signals_out, lsg_feature *features_out) {

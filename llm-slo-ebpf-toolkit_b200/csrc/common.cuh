@@ -39,6 +39,7 @@ enum {
   WS_IN3,
   WS_IN4,
   WS_FEAT,           // incident feature accumulators
+  WS_RANGES,         // per-span event ranges of the join
   WS_COUNT
 };
 
@@ -52,6 +53,20 @@ struct DevModel {
   double thresh[LSG_NSIG];
   uint32_t sig_mask;
 };
+
+#ifdef __CUDACC__
+// doubles as order-preserving unsigned keys, so that max is an integer atomicMax; key 0 is never produced by a
+// non-NaN value and stands for "absent"
+__device__ __forceinline__ unsigned long long f64_key(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double key_f64(unsigned long long k) {
+  if (k == 0) return __longlong_as_double(0x7ff8000000000000ll);
+  unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+  return __longlong_as_double((long long)b);
+}
+#endif
 
 // ---- sort key: (join group, quantised time) ------------------------------------------------------
 // live key = (grp << tbits) | ((ts - ts_min) >> shift); records that can match nothing (group 0, zero
@@ -206,8 +221,14 @@ LSG_HD uint64_t lsg_make_key(const KeySpec &k, uint32_t grp, int64_t ts) {
 // stage kernels (defined across the .cu files)
 int lsg_launch_match_pairs(lsg_ctx *, const lsg_span *, const lsg_event *, size_t, const lsg_ident *, size_t, int64_t, double,
                            const uint8_t *, const uint8_t *, uint8_t *, uint8_t *, uint64_t *eval_dev);
+struct EventColumns {     // events in key order as columns (what the join stages into shared memory)
+  const int64_t *ts;
+  const double *val;
+  const uint32_t *ident, *pid, *conn, *trsig;
+};
 struct SortedEvents {
-  const lsg_event *rec;   // events in key order
+  EventColumns col;       // set when the sort was asked for columns
+  const lsg_event *rec;   // events in key order as records (set when the sort was asked for records)
   const uint32_t *perm;   // sorted position -> input index
   const void *keys;       // sorted keys (uint32_t if key.bits <= 32 else uint64_t)
   KeySpec key;
@@ -215,6 +236,7 @@ struct SortedEvents {
   size_t n_live;          // events that can match (sorted first)
   uint64_t n_unsupported; // events with an unsupported signal type
 };
+// sorted_out != NULL: records (AoS) into sorted_out; NULL: columns (SoA) into the context workspace
 int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
                     bool exact, lsg_event *sorted_out, SortedEvents *out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,
@@ -226,8 +248,11 @@ struct JoinArgs {
   const double *attr_base; uint32_t *cand_event; uint8_t *cand_tier; double *attr_out; double *conf_out;
   double *retrieval_out; uint32_t *n_cand_out;
   uint64_t *counters;  // device: [0] matched pairs, [1] low_confidence, [2] fanout_dropped, [3] candidates, [4] kept
+  // optional fusion of the A7 glue: per (incident, signal) max keys updated straight from the join's epilogue
+  unsigned long long *inc_keys; size_t n_incidents;
 };
 int lsg_launch_join(lsg_ctx *, const JoinArgs &);
+int lsg_launch_incident_finish(lsg_ctx *, const unsigned long long *keys, size_t n_incidents, double *signals_out);
 int lsg_launch_incident_features(lsg_ctx *, const double *span_attr, const uint32_t *span_incident, const lsg_span *spans,
                                  size_t n_spans, size_t n_incidents, double *signals_out, lsg_feature *features_out);
 int lsg_launch_attribute(lsg_ctx *, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,

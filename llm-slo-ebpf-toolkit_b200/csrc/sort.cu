@@ -296,6 +296,24 @@ k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict
   }
 }
 
+// the same gather into columns: what the join stages into shared memory (ts, ident, pid, conn, trace|signal) plus values
+__global__ void __launch_bounds__(256)
+k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n, int64_t *__restrict__ ts,
+                    double *__restrict__ val, uint32_t *__restrict__ ident, uint32_t *__restrict__ pid,
+                    uint32_t *__restrict__ conn, uint32_t *__restrict__ trsig) {
+  for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t src = perm[j];
+    const uint4 a = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src));
+    const uint4 b = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src) + 1);
+    ts[j] = (int64_t)(((uint64_t)a.y << 32) | a.x);
+    val[j] = __longlong_as_double((long long)(((uint64_t)a.w << 32) | a.z));
+    ident[j] = b.x;
+    pid[j] = b.y;
+    conn[j] = b.z;
+    trsig[j] = b.w;
+  }
+}
+
 size_t scatter_smem(size_t key_bytes) {
   return (size_t)(SORT_NW * RADIX + RADIX + RADIX + 8 + SORT_TILE) * 4 + (size_t)SORT_TILE * key_bytes;
 }
@@ -441,9 +459,20 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
   }
   out->perm = perm;
   if (!sorted_out) {
+    // columns, padded so that a 16-byte aligned bulk copy may run a little past the last event
+    const size_t n_pad = ((n + 3) & ~(size_t)3) + 4;
     void *sv;
-    LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n * sizeof(lsg_event), &sv));
-    sorted_out = (lsg_event *)sv;
+    LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n_pad * 32, &sv));
+    char *base = (char *)sv;
+    int64_t *c_ts = (int64_t *)base;
+    double *c_val = (double *)(base + 8 * n_pad);
+    uint32_t *c_ident = (uint32_t *)(base + 16 * n_pad), *c_pid = (uint32_t *)(base + 20 * n_pad);
+    uint32_t *c_conn = (uint32_t *)(base + 24 * n_pad), *c_trsig = (uint32_t *)(base + 28 * n_pad);
+    ProfScope ps(ctx, PK_GATHER);
+    k_gather_events_soa<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
+    LSG_LAUNCH_CHECK(ctx);
+    out->col = EventColumns{c_ts, c_val, c_ident, c_pid, c_conn, c_trsig};
+    return 0;
   }
   {
     ProfScope ps(ctx, PK_GATHER);

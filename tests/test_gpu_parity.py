@@ -117,6 +117,34 @@ def test_edge_cases(ctx):
         ctx.process_batch(sp, ev, ids, window_ns=1 << 53)
 
 
+def test_spans_sharing_a_time_quantum(ctx):
+    """Spans are processed in (group, quantised time) order, so inside one quantum their exact times are not
+    ordered; every one of them must still see the events at the very edge of its own +-W window."""
+    W = 2_000_000_000
+    base = synth.T0_NS
+    n_s = 600
+    rng = np.random.default_rng(5)
+    sp = np.zeros(n_s, A.SPAN_DTYPE)
+    sp["ts_ns"] = base + 10 * W + np.sort(rng.integers(0, 1 << 24, n_s))[::-1]    # decreasing inside quanta
+    sp["ts_ns"][::7] += 1 << 25
+    sp["ident"], sp["pid"], sp["conn"], sp["trace"], sp["incident"] = 0, 7, 3, np.arange(1, n_s + 1), A.NONE
+    ev = np.zeros(4 * n_s + 5000, A.EVENT_DTYPE)
+    k = np.arange(n_s)
+    for r, dt in enumerate((W, -W, W - 1, -(W - 1))):                              # both edges, inclusive
+        ev["ts_ns"][r * n_s + k] = sp["ts_ns"] + dt
+        ev["trace_sig"][r * n_s + k] = (sp["trace"] << 4) | (r % 10)
+    fill = slice(4 * n_s, None)                                                    # filler so that tiles have to be cut
+    ev["ts_ns"][fill] = base + rng.integers(0, 20 * W, 5000)
+    ev["trace_sig"][fill] = 2
+    ev["pid"][fill] = 7
+    ev["ident"], ev["value"] = 0, rng.random(len(ev))
+    ids = np.array([(1, 1, 1, 1)], A.IDENT_DTYPE)
+    got = ctx.process_batch(sp, ev, ids, W, 0.7, 8)
+    want = O.process_batch(sp, ev, ids, W, 0.7, 8, indexed=False, nthreads=8)
+    _eq_batch(got, want)
+    assert (got["n_cand"] >= 4).all()
+
+
 def test_match_pairs_vs_oracle(ctx):
     cfg = synth.config(100_000, 20_000, 16, 8, 2, seed=3, horizon_ns=40_000_000_000)
     w = synth.generate_host(cfg)
@@ -293,6 +321,12 @@ def test_full_c2_properties(ctx):
     unsup = int(((ev["trace_sig"] & 15) >= A.NSIG).sum())
     assert c.debug.unsupported_type == unsup * ns
     assert c.debug.unmatched + c.debug.low_confidence + c.candidates == (cfg.n_events - unsup) * ns
+    # the whole batch against the indexed CPU oracle (a few seconds on the host cores)
+    w = synth.generate_host(cfg)
+    j = O.process_batch(w["spans"], w["events"], w["idents"], indexed=True, nthreads=O.hw_threads())
+    assert c.debug.as_tuple() == j["debug"].as_tuple()
+    assert c.candidates == int(j["n_cand"].sum())
+    assert np.array_equal(cand, j["cand_event"]) and np.array_equal(tier, j["cand_tier"])
     # sampled join groups, exact
     sp, ids = d.host("spans", A.SPAN_DTYPE), d.host("idents", A.IDENT_DTYPE)
     attr = d.host("attr", np.float64, (ns, A.NSIG))
