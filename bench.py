@@ -296,7 +296,8 @@ def main():
     alg = {   # algorithmic bytes per launch: every operand read once, every result written once
         "event_stats": 32 * n, "event_keys": (32 + key_bytes) * n, "radix_hist": key_bytes * n,
         "radix_scatter": 2 * (key_bytes + 4) * n, "gather_events": (4 + 32 + 32) * n,
-        "join": 32 * n + (key_bytes + 4) * n + 32 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),
+        "join": 28 * n + 32 * s_ + 8 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # six columns once, span, range, outputs
+        "span_ranges": 32 * s_ + 8 * s_ + key_bytes * n,
         "incident_features": A.NSIG * 8 * s_ + 4 * s_ + 2 * A.NSIG * 8 * i_, "attribute": (A.NSIG * 8 + A.NDOM * 8 + 1) * i_,
         "confusion": (A.NDOM * 8 + 7) * i_,
     }

@@ -231,7 +231,7 @@ void lsg_destroy(lsg_ctx *ctx) {
 // ---- per-kernel timing ------------------------------------------------------------------------------
 static const char *kProfNames[PK_COUNT] = {"event_stats", "event_keys", "radix_hist", "radix_scan", "radix_scatter",
                                            "gather_events", "span_sort", "join", "incident_features", "attribute",
-                                           "confusion", "match_pairs"};
+                                           "confusion", "match_pairs", "span_ranges"};
 int lsg_profile_enable(lsg_ctx *ctx, int on) {
   if (!ctx) return LSG_ERR_INVALID;
   ctx->prof = on != 0;

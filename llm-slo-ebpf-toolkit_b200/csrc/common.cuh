@@ -83,7 +83,7 @@ struct KeySpec {
 // per-kernel timing (bench.py's roofline): CUDA events recorded on the context's stream around each launch
 enum {
   PK_STATS = 0, PK_KEYS, PK_HIST, PK_SCAN, PK_SCATTER, PK_GATHER, PK_SPAN_SORT, PK_JOIN, PK_FEATURES, PK_ATTRIBUTE,
-  PK_CONFUSION, PK_PAIRS, PK_COUNT
+  PK_CONFUSION, PK_PAIRS, PK_RANGES, PK_COUNT
 };
 struct ProfSpan { int kind; cudaEvent_t a, b; };
 

@@ -11,11 +11,16 @@
 // order nor the time quantisation can change the result.
 //
 // Two kernels:
-//   k_span_ranges  one thread per span (in key order): binary search of its [a, b) in the sorted keys.
+//   k_span_ranges  one thread per span (in key order): binary search of its outer range [a, b) (|dt| <= W, the
+//                  only place a trace-id match can be) and inner range [a2, b2) (|dt| <= min(W, 500 ms), the
+//                  only place tiers 2-4 can be) in the sorted keys.
 //   k_join_tiles   a CTA takes 128 consecutive spans.  Their ranges overlap heavily (each event is inside
-//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — five columns,
-//                  24 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier)
-//                  and its 8 warps scan their spans' windows out of shared memory, one warp per span.
+//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — six columns,
+//                  28 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier)
+//                  and its 8 warps scan their spans' windows out of shared memory, one warp per span:
+//                  a 128-bit vectorised pass over the trace|signal column of [a, b) (tier 1), the full
+//                  decision only over [a2, b2), candidates appended to a per-warp list by ballot
+//                  compaction, best `fanout` picked at the end with warp REDUX minima.
 //                  HBM/L2 traffic drops from ~11 KB to ~0.5 KB per span.  A span whose own range does
 //                  not fit a tile is scanned straight from global memory by the same code.
 // Outputs are written at the span's input position; optionally the per-incident maxima (A7 glue) are
@@ -37,7 +42,7 @@ struct JoinParams {
   size_t n_spans;
   EventColumns ev;
   const uint32_t *ev_perm;   // sorted position -> input index
-  const uint2 *ranges;       // per span in key order: [a, b) in sorted positions
+  const uint4 *ranges;       // per span in key order: outer [x, y) and inner [z, w) in sorted positions
   const lsg_ident *idents;
   uint32_t n_idents;
   int64_t window_ns;
@@ -70,12 +75,12 @@ template <typename KeyT>
 __global__ void __launch_bounds__(256)
 k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ span_perm, size_t n_spans,
               const KeyT *__restrict__ keys, uint32_t n_live, KeySpec ks, const lsg_ident *__restrict__ idents,
-              uint32_t n_idents, int64_t W, uint2 *__restrict__ ranges, unsigned long long *__restrict__ counters) {
+              uint32_t n_idents, int64_t W, uint4 *__restrict__ ranges, unsigned long long *__restrict__ counters) {
   const uint64_t ts_max_q = ((uint64_t)1 << ks.tbits) - 1;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_spans; q += (size_t)gridDim.x * blockDim.x) {
     const size_t si = span_perm ? span_perm[q] : q;
     const SpanRec s = load_span(spans + si);
-    uint2 r = make_uint2(n_live, n_live);
+    uint4 r = make_uint4(n_live, n_live, n_live, n_live);
     if (s.ident >= n_idents) {
       atomicOr((unsigned int *)&counters[5], 1u);
     } else {
@@ -91,48 +96,25 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
         const uint64_t qs = ((uint64_t)tc - (uint64_t)ks.ts_min) >> ks.shift;
         const int64_t t0 = (int64_t)((uint64_t)ks.ts_min + (qs << ks.shift));
         const int64_t t1 = (int64_t)((uint64_t)t0 + (((uint64_t)1 << ks.shift) - 1));
-        const int64_t t_lo = t0 < INT64_MIN + W ? INT64_MIN : t0 - W;
-        const int64_t t_hi = t1 > INT64_MAX - W ? INT64_MAX : t1 + W;
-        const uint64_t qlo = t_lo <= ks.ts_min ? 0 : (((uint64_t)t_lo - (uint64_t)ks.ts_min) >> ks.shift);
-        uint64_t qhi = ((uint64_t)t_hi - (uint64_t)ks.ts_min) >> ks.shift;   // t_hi >= t1 >= ts_min
-        if (qhi > ts_max_q) qhi = ts_max_q;
-        const KeyT klo = (KeyT)(((uint64_t)grp << ks.tbits) | qlo);
-        const KeyT khi = (KeyT)(((uint64_t)grp << ks.tbits) | qhi);
-        r.x = lower_bound_keys<KeyT>(keys, n_live, klo);
-        r.y = lower_bound_keys<KeyT>(keys, n_live, (KeyT)(khi + 1));
+        auto search = [&](const int64_t w, uint32_t lo_pos, uint32_t hi_pos, uint32_t *pa, uint32_t *pb) {
+          const int64_t t_lo = t0 < INT64_MIN + w ? INT64_MIN : t0 - w;
+          const int64_t t_hi = t1 > INT64_MAX - w ? INT64_MAX : t1 + w;
+          const uint64_t qlo = t_lo <= ks.ts_min ? 0 : (((uint64_t)t_lo - (uint64_t)ks.ts_min) >> ks.shift);
+          uint64_t qhi = ((uint64_t)t_hi - (uint64_t)ks.ts_min) >> ks.shift;   // t_hi >= t1 >= ts_min
+          if (qhi > ts_max_q) qhi = ts_max_q;
+          const KeyT klo = (KeyT)(((uint64_t)grp << ks.tbits) | qlo);
+          const KeyT khi = (KeyT)(((uint64_t)grp << ks.tbits) | qhi);
+          *pa = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, klo);
+          *pb = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, (KeyT)(khi + 1));
+        };
+        search(W, 0, n_live, &r.x, &r.y);
+        const int64_t Wi = W < 500 * kMs ? W : 500 * kMs;          // tiers 2-4: dns.go:62-73
+        search(Wi, r.x, r.y, &r.z, &r.w);                           // inside the outer range: a short search
       }
     }
     ranges[q] = r;
   }
 }
-
-// ---- best-F candidates under the reference's order ----------------------------------------------------
-template <int F>
-struct TopF {
-  uint64_t k1[F];   // (tier << 56) | |dt|
-  uint32_t idx[F];  // input index of the event
-  uint32_t pos[F];  // sorted position of the event
-  __device__ __forceinline__ void init() {
-#pragma unroll
-    for (int i = 0; i < F; ++i) { k1[i] = ~0ull; idx[i] = 0xffffffffu; pos[i] = 0xffffffffu; }
-  }
-  __device__ __forceinline__ void insert(uint64_t k, uint32_t ix, uint32_t ps) {
-#pragma unroll
-    for (int i = 0; i < F; ++i) {
-      const bool less = k < k1[i] || (k == k1[i] && ix < idx[i]);
-      if (less) {
-        uint64_t tk = k1[i]; k1[i] = k; k = tk;
-        uint32_t ti = idx[i]; idx[i] = ix; ix = ti;
-        uint32_t tp = pos[i]; pos[i] = ps; ps = tp;
-      }
-    }
-  }
-  __device__ __forceinline__ void pop() {
-#pragma unroll
-    for (int i = 0; i + 1 < F; ++i) { k1[i] = k1[i + 1]; idx[i] = idx[i + 1]; pos[i] = pos[i + 1]; }
-    k1[F - 1] = ~0ull; idx[F - 1] = 0xffffffffu; pos[F - 1] = 0xffffffffu;
-  }
-};
 
 // ---- TMA bulk copy + mbarrier (global -> shared, completion counted in bytes) ---------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -155,101 +137,169 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-struct JoinSmem {
-  int64_t ts[JT_CAP];
-  uint32_t ident[JT_CAP];
-  uint32_t pid[JT_CAP];
-  uint32_t conn[JT_CAP];
-  uint32_t trsig[JT_CAP];
-  uint4 span[JT_CH][2];
-  uint32_t a[JT_CH], b[JT_CH], sidx[JT_CH];
-  unsigned long long cnt[5];
-  uint64_t bar;
+constexpr int JT_LIST = 64;    // per-warp candidate list (entries); compacted to the best `fanout` when it fills
+
+struct Cand {
+  uint64_t k1;    // (tier << 56) | |dt|: the reference's order, correlator.go:92-99
+  uint32_t idx;   // input index of the event: ties keep input order (sort.SliceStable)
+  uint32_t pos;   // sorted position of the event
 };
 
-// the five columns a scan reads, either the shared-memory tile (base = first staged position) or global memory (base 0)
+// the columns a scan reads, either the shared-memory tile (base = first staged position) or global memory (base 0)
 struct Cols {
   const int64_t *ts;
-  const uint32_t *ident, *pid, *conn, *trsig;
+  const uint32_t *ident, *pid, *conn, *trsig, *perm;
   uint32_t base;
 };
 
-// One span, one warp: scan [a, b), select, write.  Counters go to the caller's per-lane accumulators.
-template <int F>
-__device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, const SpanRec s, const size_t si, const uint32_t a,
-                                             const uint32_t b, const unsigned lane, unsigned long long &w_matched,
+__device__ __forceinline__ bool cand_less(uint64_t ka, uint32_t ia, uint64_t kb, uint32_t ib) {
+  return ka < kb || (ka == kb && ia < ib);
+}
+
+// Best `want` entries of list[0, n) in order; lane r ends up holding the r-th.  Returns how many there are.
+__device__ __forceinline__ int select_best(const Cand *list, const int n, const int want, const unsigned lane, uint64_t &my_k,
+                                           uint32_t &my_idx, uint32_t &my_pos) {
+  // every lane owns entries lane and lane + 32 (n <= JT_LIST = 64)
+  Cand e0{~0ull, 0xffffffffu, 0xffffffffu}, e1 = e0;
+  if ((int)lane < n) e0 = list[lane];
+  if ((int)lane + 32 < n) e1 = list[lane + 32];
+  my_k = ~0ull; my_idx = LSG_NONE; my_pos = 0xffffffffu;
+  int kept = 0;
+  for (int r = 0; r < want; ++r) {
+    const bool second = cand_less(e1.k1, e1.idx, e0.k1, e0.idx);
+    const uint64_t k = second ? e1.k1 : e0.k1;
+    const uint32_t ix = second ? e1.idx : e0.idx, ps = second ? e1.pos : e0.pos;
+    // lexicographic warp minimum of (k.hi, k.lo, idx): three REDUX steps
+    const uint32_t hi = (uint32_t)(k >> 32), lo = (uint32_t)k;
+    const uint32_t mhi = __reduce_min_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    const uint32_t mi = __reduce_min_sync(0xffffffffu, (hi == mhi && lo == mlo) ? ix : 0xffffffffu);
+    const uint64_t mk = ((uint64_t)mhi << 32) | mlo;
+    if (mk == ~0ull) break;
+    const bool mine = k == mk && ix == mi;
+    const unsigned owner = __ffs(__ballot_sync(0xffffffffu, mine)) - 1;
+    const uint32_t wpos = __shfl_sync(0xffffffffu, ps, owner);
+    if (mine) {
+      if (second) e1.k1 = ~0ull, e1.idx = 0xffffffffu; else e0.k1 = ~0ull, e0.idx = 0xffffffffu;
+    }
+    if ((int)lane == r) { my_k = mk; my_idx = mi; my_pos = wpos; }
+    kept++;
+  }
+  return kept;
+}
+
+// One span, one warp: scan, select, write.  Counters go to the caller's per-lane accumulators.
+__device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, Cand *list, const SpanRec s, const size_t si,
+                                             const uint4 rg, const unsigned lane, unsigned long long &w_matched,
                                              unsigned long long &w_low, unsigned long long &w_drop, unsigned long long &w_cand,
                                              unsigned long long &w_kept) {
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  TopF<F> top;
-  top.init();
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const uint64_t W = (uint64_t)p.window_ns;
   unsigned n_cand = 0, n_match = 0, n_low = 0;
-  if (a < b) {
-    const lsg_ident sid = load_ident(p.idents, s.ident);
-    const uint64_t W = (uint64_t)p.window_ns;
-    for (uint32_t j = a + lane; j < b; j += 32) {
-      const uint32_t o = j - c.base;
-      const uint64_t adt = lsg_absdiff(s.ts, c.ts[o]);
-      if (adt > W) continue;   // outer window, dns.go:54-56 (the quantised range is only a superset)
-      const uint32_t trsig = c.trsig[o];
-      int tier = 0;
-      if (s.trace != 0 && s.trace == (trsig >> 4)) {
-        tier = LSG_TIER_TRACE;                                       // dns.go:58-60
-      } else if (adt <= (uint64_t)(500 * kMs)) {                     // tiers 2-4 all need |dt| <= 500 ms
-        const uint32_t e_ident = c.ident[o];
-        lsg_ident eid = sid;
-        if (e_ident != s.ident) eid = load_ident(p.idents, e_ident);
-        tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, c.pid[o], c.conn[o], eid);
-      }
-      if (tier == 0) continue;   // Unmatched (counted analytically by the caller)
-      n_match++;
-      if (lsg_tier_conf(tier) < p.threshold) { n_low++; continue; }   // correlator.go:83-86
-      n_cand++;
-      top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[j], j);
+  int n_list = 0;   // warp-uniform
+  uint64_t my_k;
+  uint32_t my_idx, my_pos;
+
+  // append the lanes that have a candidate to the warp's list (warp-uniform control flow around it)
+  auto append = [&](const bool has, const uint64_t k1, const uint32_t o, const uint32_t j) {
+    const unsigned m = __ballot_sync(0xffffffffu, has);
+    if (m == 0) return;
+    if (n_list + 32 > JT_LIST) {   // keep only what can still win
+      __syncwarp();
+      const int kept = select_best(list, n_list, p.fanout, lane, my_k, my_idx, my_pos);
+      __syncwarp();
+      if ((int)lane < kept) list[lane] = Cand{my_k, my_idx, my_pos};
+      n_list = kept;
+      __syncwarp();
     }
-  }
-  for (int o = 16; o; o >>= 1) {
-    n_cand += __shfl_xor_sync(0xffffffffu, n_cand, o);
-    n_match += __shfl_xor_sync(0xffffffffu, n_match, o);
-    n_low += __shfl_xor_sync(0xffffffffu, n_low, o);
-  }
-  // merge the lanes' best-F lists into the span's best `fanout` (reference order)
-  uint32_t my_idx = LSG_NONE, my_pos = 0xffffffffu;
-  unsigned my_tier = 0, first_tier = 0;
-  const int want = p.fanout < F ? p.fanout : F;
-  int kept = 0;
-  if (n_cand != 0) {
-    for (int r = 0; r < want; ++r) {
-      uint64_t mk = top.k1[0];
-      uint32_t mi = top.idx[0];
+    if (has) list[n_list + __popc(m & lt_mask)] = Cand{k1, c.perm[o], j};
+    n_list += __popc(m);
+    n_cand += __popc(m);   // warp-uniform running total
+  };
+
+  if (rg.x < rg.y) {
+    // ---- tier 1 (dns.go:58-60): a trace-id match can sit anywhere in the outer window.  Only the trace|signal
+    //      column is read, four events per lane and load; the time is looked at for hits only.
+    if (s.trace != 0) {
+      const uint32_t v0 = (rg.x - c.base) & ~3u, v_end = rg.y - c.base, v_beg = rg.x - c.base;
+      for (uint32_t vb = v0; vb < v_end; vb += 128) {
+        const uint32_t v = vb + lane * 4;
+        uint4 q = make_uint4(0, 0, 0, 0);
+        if (v < v_end) q = *reinterpret_cast<const uint4 *>(c.trsig + v);   // 16-byte aligned; the tile is padded past its end
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-      for (int o = 16; o; o >>= 1) {
-        const uint64_t ok = __shfl_xor_sync(0xffffffffu, mk, o);
-        const uint32_t oi = __shfl_xor_sync(0xffffffffu, mi, o);
-        if (ok < mk || (ok == mk && oi < mi)) { mk = ok; mi = oi; }
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t o = v + e;
+          bool hit = o >= v_beg && o < v_end && (w[e] >> 4) == s.trace;
+          uint64_t adt = 0;
+          if (hit) {
+            adt = lsg_absdiff(s.ts, c.ts[o]);
+            hit = adt <= W;                                   // outer window, dns.go:54-56
+          }
+          if (__any_sync(0xffffffffu, hit)) {
+            n_match += __popc(__ballot_sync(0xffffffffu, hit));
+            const bool low = hit && 1.0 < p.threshold;       // confidence 1.0 below the threshold (threshold > 1)
+            n_low += __popc(__ballot_sync(0xffffffffu, low));
+            append(hit && !low, ((uint64_t)LSG_TIER_TRACE << 56) | adt, o, o + c.base);
+          }
+        }
       }
-      if (mk == ~0ull) break;
-      const bool mine = top.k1[0] == mk && top.idx[0] == mi;
-      const unsigned owner = __ffs(__ballot_sync(0xffffffffu, mine)) - 1;
-      const uint32_t ps = __shfl_sync(0xffffffffu, top.pos[0], owner);
-      if (mine) top.pop();
-      if ((int)lane == r) { my_idx = mi; my_pos = ps; my_tier = (unsigned)(mk >> 56); }
-      if (r == 0) first_tier = (unsigned)(mk >> 56);
-      kept++;
+    }
+    // ---- tiers 2-4 (dns.go:61-73) need |dt| <= 500 ms: the inner range only; trace-id matches were taken above
+    if (rg.z < rg.w) {
+      const lsg_ident sid = load_ident(p.idents, s.ident);
+      const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
+      for (uint32_t jb = rg.z; jb < rg.w; jb += 32) {
+        const uint32_t j = jb + lane;
+        int tier = 0;
+        uint64_t adt = 0;
+        uint32_t o = 0;
+        if (j < rg.w) {
+          o = j - c.base;
+          adt = lsg_absdiff(s.ts, c.ts[o]);
+          const uint32_t trsig = c.trsig[o];
+          if (adt <= Wi && !(s.trace != 0 && s.trace == (trsig >> 4))) {
+            const uint32_t e_ident = c.ident[o];
+            lsg_ident eid = sid;
+            if (e_ident != s.ident) eid = load_ident(p.idents, e_ident);
+            tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, c.pid[o], c.conn[o], eid);
+          }
+        }
+        const bool is_m = tier != 0;
+        const unsigned mm = __ballot_sync(0xffffffffu, is_m);
+        if (mm) {
+          const bool low = is_m && lsg_tier_conf(tier) < p.threshold;   // correlator.go:83-86
+          n_match += __popc(mm);
+          n_low += __popc(__ballot_sync(0xffffffffu, low));
+          append(is_m && !low, ((uint64_t)tier << 56) | adt, o, j);
+        }
+      }
     }
   }
-  // kept candidates in order (correlator.go:101-104)
+  // ---- the span's best `fanout` candidates in the reference's order (correlator.go:92-104)
+  __syncwarp();
+  const int kept = select_best(list, n_list, p.fanout, lane, my_k, my_idx, my_pos);
+  __syncwarp();
+  const unsigned my_tier = my_idx == LSG_NONE ? 0u : (unsigned)(my_k >> 56);
+  const unsigned first_tier = __shfl_sync(0xffffffffu, my_tier, 0);
   if ((int)lane < p.fanout) {
     p.cand_event[si * (size_t)p.fanout + lane] = my_idx;
     p.cand_tier[si * (size_t)p.fanout + lane] = (uint8_t)my_tier;
   }
-  // per-attribute max over the kept candidates (correlator.go:106-112): lane s owns signal s
+  // per-attribute max over the kept candidates (correlator.go:106-112): lane s owns signal s.
+  // lane r < kept fetches its own candidate's value and signal (independent loads, one latency), then broadcasts
   double val = nan;
   if (lane < LSG_NSIG && p.attr_base) val = p.attr_base[si * LSG_NSIG + lane];
+  double my_val = 0.0;
+  unsigned my_sig = 0xffu;
+  if ((int)lane < kept) {
+    my_val = p.ev.val[my_pos];
+    my_sig = p.ev.trsig[my_pos] & 15u;
+  }
   for (int r = 0; r < kept; ++r) {
-    const uint32_t ps = __shfl_sync(0xffffffffu, my_pos, r);
-    const double v = p.ev.val[ps];                     // same address in every lane: one broadcast load
-    const unsigned sig = p.ev.trsig[ps] & 15u;
+    const double v = __shfl_sync(0xffffffffu, my_val, r);
+    const unsigned sig = __shfl_sync(0xffffffffu, my_sig, r);
     if (sig == lane && (isnan(val) || v > val)) val = v;
   }
   if (lane < LSG_NSIG) {
@@ -284,27 +334,89 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
   return s;
 }
 
+// ---- the tile kernel: two threads per span -------------------------------------------------------------
+// A warp that serves one span pays a vote or ballot for every rare event.  Here each span gets two threads
+// (lanes 2k, 2k+1): each scans half of the span's outer range for trace-id hits (128-bit loads of the
+// trace|signal column) and half of its inner range with the full tier 2-4 decision, out of the shared tile,
+// with plain per-thread code.  Hits are only noted — two bytes (tier, tile offset) in a per-thread list —
+// and ordered afterwards in registers, when every lane of the warp is doing the same thing; the two
+// halves are merged with shuffles.  Attribute rows go through a shared staging buffer so that the 96-byte
+// rows leave as coalesced stores.
+constexpr int TM_CAP = 1920;    // events per tile
+constexpr int TM_LIST = 16;     // noted hits per thread before they are condensed to the best `fanout`
+
 template <int F>
-__global__ void __launch_bounds__(JT_THREADS)
-k_join_tiles(const __grid_constant__ JoinParams p) {
+struct TopF {
+  uint64_t k1[F];   // (tier << 56) | |dt|
+  uint32_t idx[F];  // input index of the event
+  uint32_t pos[F];  // sorted position of the event
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int i = 0; i < F; ++i) { k1[i] = ~0ull; idx[i] = 0xffffffffu; pos[i] = 0xffffffffu; }
+  }
+  __device__ __forceinline__ void insert(uint64_t k, uint32_t ix, uint32_t ps) {
+#pragma unroll
+    for (int i = 0; i < F; ++i) {
+      const bool less = k < k1[i] || (k == k1[i] && ix < idx[i]);
+      if (less) {
+        uint64_t tk = k1[i]; k1[i] = k; k = tk;
+        uint32_t ti = idx[i]; idx[i] = ix; ix = ti;
+        uint32_t tp = pos[i]; pos[i] = ps; ps = tp;
+      }
+    }
+  }
+};
+
+struct TileSmem {
+  int64_t ts[TM_CAP];
+  uint32_t ident[TM_CAP];
+  uint32_t pid[TM_CAP];
+  uint32_t conn[TM_CAP];
+  uint32_t trsig[TM_CAP];
+  uint4 span[JT_CH][2];
+  uint4 rng[JT_CH];
+  uint32_t sidx[JT_CH];
+  uint16_t note[TM_LIST][JT_THREADS];   // entry-major: consecutive lanes, consecutive halfwords
+  double stage[JT_CH][LSG_NSIG];        // attribute rows of the chunk
+  unsigned long long cnt[5];
+  uint64_t bar;
+};
+
+// order the noted hits of one thread: exact |dt| from the tile, input index from the permutation
+template <int F>
+__device__ __forceinline__ void order_notes(const TileSmem &sm, const JoinParams &p, const unsigned tid, const int n,
+                                            const int64_t s_ts, const uint32_t base, TopF<F> &top) {
+#pragma unroll 4
+  for (int i = 0; i < n; ++i) {
+    const uint32_t e = sm.note[i][tid];
+    const uint32_t o = e & 0xfffu, tier = e >> 12;
+    const uint64_t adt = lsg_absdiff(s_ts, sm.ts[o]);
+    top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[base + o], base + o);
+  }
+}
+
+template <int F>
+__global__ void __launch_bounds__(JT_THREADS, 3)
+k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  JoinSmem &sm = *reinterpret_cast<JoinSmem *>(smem_raw);
-  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  TileSmem &sm = *reinterpret_cast<TileSmem *>(smem_raw);
+  const unsigned tid = threadIdx.x, lane = tid & 31;
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
   if (tid < 5) sm.cnt[tid] = 0;
   if (tid == 0) mbar_init(&sm.bar, 1);
   __syncthreads();
   uint32_t phase = 0;
   unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
   const size_t n_chunks = (p.n_spans + JT_CH - 1) / JT_CH;
+  const uint64_t W = (uint64_t)p.window_ns;
+  const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
 
   for (size_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
     const size_t q0 = chunk * JT_CH;
     const int nq = (int)min((size_t)JT_CH, p.n_spans - q0);
-    // stage the chunk's spans: input index, range, record (two 16-byte halves per span)
+    // stage the chunk's spans: input index, ranges, record (two 16-byte halves per span), attribute rows
     if ((int)tid < nq) {
-      const uint2 r = p.ranges[q0 + tid];
-      sm.a[tid] = r.x;
-      sm.b[tid] = r.y;
+      sm.rng[tid] = p.ranges[q0 + tid];
       sm.sidx[tid] = p.span_perm ? p.span_perm[q0 + tid] : (uint32_t)(q0 + tid);
     }
     {
@@ -315,25 +427,25 @@ k_join_tiles(const __grid_constant__ JoinParams p) {
       }
     }
     __syncthreads();
+    for (int i = tid; i < nq * LSG_NSIG; i += JT_THREADS) {
+      const int r = i / LSG_NSIG, col = i - r * LSG_NSIG;
+      sm.stage[r][col] = p.attr_base ? p.attr_base[(size_t)sm.sidx[r] * LSG_NSIG + col] : nan;
+    }
     int i0 = 0;
     while (i0 < nq) {
-      const uint32_t A = sm.a[i0] & ~3u;   // 16-byte aligned start for every column
-      // spans of the chunk whose range still ends inside a tile that starts at A (b is non-decreasing)
-      const bool fits = (int)tid >= i0 && (int)tid < nq && sm.b[tid] - A <= (uint32_t)(JT_CAP - 4);
+      const uint32_t A = sm.rng[i0].x & ~3u;   // 16-byte aligned start for every column
+      // spans of the chunk whose outer range still ends inside a tile that starts at A (ranges are monotone)
+      const bool fits = (int)tid >= i0 && (int)tid < nq && sm.rng[tid].y - A <= (uint32_t)(TM_CAP - 4);
       const int n_fit = __syncthreads_count(fits);
       if (n_fit == 0) {
-        // this span's own range is larger than a tile: scan it from global memory
-        if (warp == 0) {
-          const SpanRec s = span_from_halves(sm.span[i0][0], sm.span[i0][1]);
-          const Cols g{p.ev.ts, p.ev.ident, p.ev.pid, p.ev.conn, p.ev.trsig, 0u};
-          process_span<F>(p, g, s, sm.sidx[i0], sm.a[i0], sm.b[i0], lane, w_matched, w_low, w_drop, w_cand, w_kept);
-        }
+        // this span's own range is larger than a tile: leave it to k_join_big
+        if (tid == 0) big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q0 + i0);
         i0 += 1;
         continue;
       }
       const int i1 = i0 + n_fit;
-      const uint32_t Bend = (sm.b[i1 - 1] + 3u) & ~3u;
-      const uint32_t count = Bend > A ? Bend - A : 0;   // <= JT_CAP, multiple of 4; the columns are padded past n
+      const uint32_t Bend = (sm.rng[i1 - 1].y + 3u) & ~3u;
+      const uint32_t count = Bend > A ? Bend - A : 0;   // <= TM_CAP, multiple of 4; the columns are padded past n
       if (count) {
         if (tid == 0) {
           mbar_expect_tx(&sm.bar, count * 24u);
@@ -346,15 +458,154 @@ k_join_tiles(const __grid_constant__ JoinParams p) {
         mbar_wait(&sm.bar, phase);
         phase ^= 1;
       }
-      const Cols c{sm.ts, sm.ident, sm.pid, sm.conn, sm.trsig, A};
-      for (int k = i0 + (int)warp; k < i1; k += JT_WARPS) {
-        const SpanRec s = span_from_halves(sm.span[k][0], sm.span[k][1]);
-        process_span<F>(p, c, s, sm.sidx[k], sm.a[k], sm.b[k], lane, w_matched, w_low, w_drop, w_cand, w_kept);
+      // ---- scan: thread (2k + h) takes half h of span k's ranges; 128 spans per round of the block
+      for (int kb = i0; kb < i1; kb += JT_THREADS / 2) {
+        const int k = kb + (int)(tid >> 1);
+        const unsigned h = tid & 1;
+        const bool live = k < i1;
+        unsigned n_cand = 0, n_match = 0, n_low = 0;
+        int n_note = 0;
+        SpanRec s;
+        s.ts = 0; s.ident = 0; s.pid = 0; s.conn = 0; s.trace = 0; s.incident = LSG_NONE;
+        TopF<F> top;
+        top.init();
+        if (live) {
+          s = span_from_halves(sm.span[k][0], sm.span[k][1]);
+          const uint4 rg = sm.rng[k];
+          // note a hit; when the list is full, condense it to the entries that can still win
+          auto note = [&](const uint32_t tier, const uint32_t o) {
+            if (n_note == TM_LIST) {
+              TopF<F> t2;
+              t2.init();
+              order_notes<F>(sm, p, tid, n_note, s.ts, A, t2);
+              n_note = 0;
+#pragma unroll
+              for (int r = 0; r < F; ++r)
+                if (t2.idx[r] != 0xffffffffu && r < p.fanout)
+                  sm.note[n_note++][tid] = (uint16_t)(((uint32_t)(t2.k1[r] >> 56) << 12) | (t2.pos[r] - A));
+            }
+            sm.note[n_note++][tid] = (uint16_t)((tier << 12) | o);
+            n_cand++;
+          };
+          if (rg.x < rg.y) {
+            // tier 1 (dns.go:58-60): trace-id equality anywhere in the outer window; 4 events per 128-bit load
+            if (s.trace != 0) {
+              const uint32_t xo = rg.x - A, yo = rg.y - A;
+              const uint32_t mid = (xo + ((yo - xo) >> 1) + 3u) & ~3u;      // both halves start 16-byte aligned
+              const uint32_t beg = h ? min(mid, yo) : xo, end = h ? yo : min(mid, yo);
+              for (uint32_t v = beg & ~3u; v < end; v += 4) {
+                const uint4 q = *reinterpret_cast<const uint4 *>(sm.trsig + v);
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const uint32_t o = v + e;
+                  if ((w[e] >> 4) == s.trace && o >= beg && o < end) {
+                    const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
+                    if (adt <= W) {                                  // outer window, dns.go:54-56
+                      n_match++;
+                      if (1.0 < p.threshold) n_low++; else note(LSG_TIER_TRACE, o);
+                    }
+                  }
+                }
+              }
+            }
+            // tiers 2-4 (dns.go:61-73) need |dt| <= 500 ms: the inner range; trace-id matches were taken above
+            if (rg.z < rg.w) {
+              const lsg_ident sid = load_ident(p.idents, s.ident);
+              const uint32_t zo = rg.z - A, wo = rg.w - A;
+              const uint32_t mid = zo + ((wo - zo) >> 1);
+              const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
+              for (uint32_t o = beg; o < end; ++o) {
+                const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
+                if (adt > Wi) continue;
+                const uint32_t trsig = sm.trsig[o];
+                if (s.trace != 0 && s.trace == (trsig >> 4)) continue;
+                const uint32_t e_ident = sm.ident[o];
+                lsg_ident eid = sid;
+                if (e_ident != s.ident) eid = load_ident(p.idents, e_ident);
+                const int tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, sm.pid[o], sm.conn[o], eid);
+                if (tier == 0) continue;                             // Unmatched: counted analytically by the caller
+                n_match++;
+                if (lsg_tier_conf(tier) < p.threshold) n_low++;      // correlator.go:83-86
+                else note((uint32_t)tier, o);
+              }
+            }
+          }
+        }
+        // ---- order: every lane sorts its own notes, then the odd lane hands its best F to the even lane
+        order_notes<F>(sm, p, tid, n_note, s.ts, A, top);
+#pragma unroll
+        for (int r = 0; r < F; ++r) {
+          const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
+          const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
+          const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
+          if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
+        }
+        n_cand += __shfl_down_sync(0xffffffffu, n_cand, 1);
+        n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
+        n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
+        // ---- write: the even lane owns the span
+        int kept = 0;
+        if (live && !h) {
+          const size_t si = sm.sidx[k];
+          double *row = sm.stage[k];
+          double vals[F];
+#pragma unroll
+          for (int r = 0; r < F; ++r) vals[r] = (r < p.fanout && top.idx[r] != 0xffffffffu) ? p.ev.val[top.pos[r]] : 0.0;
+#pragma unroll
+          for (int r = 0; r < F; ++r) {
+            if (r < p.fanout) {
+              const bool has = top.idx[r] != 0xffffffffu;
+              p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
+              p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
+              if (has) {
+                kept++;
+                const unsigned sig = sm.trsig[top.pos[r] - A] & 15u;                        // per-attribute max, correlator.go:106-112
+                const double cur = row[sig];
+                if (isnan(cur) || vals[r] > cur) row[sig] = vals[r];
+              }
+            }
+          }
+          // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
+          p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
+          if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
+            double total = 0.0;
+            if (!isnan(row[0])) total += row[0];
+            if (!isnan(row[3])) total += row[3];
+            if (!isnan(row[4])) total += row[4];
+            p.retrieval_out[si] = total;
+          }
+          if (p.n_cand_out) p.n_cand_out[si] = n_cand;
+          w_matched += n_match;
+          w_low += n_low;
+          w_cand += n_cand;
+          w_kept += kept;
+          if (n_cand > (unsigned)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
+        }
       }
-      __syncthreads();   // every warp is done with the tile before the next bulk copy overwrites it
+      __syncthreads();   // every thread is done with the tile before the next bulk copy overwrites it
       i0 = i1;
     }
-    __syncthreads();     // and with the chunk's span staging before the next chunk
+    // ---- the chunk's attribute rows leave as coalesced 96-byte rows; per-incident maxima (A7) ride along
+    for (int i = tid; i < nq * LSG_NSIG; i += JT_THREADS) {
+      const int r = i / LSG_NSIG, col = i - r * LSG_NSIG;
+      const uint4 rg = sm.rng[r];
+      if (rg.y - (rg.x & ~3u) > (uint32_t)(TM_CAP - 4)) continue;        // left to k_join_big
+      const double v = sm.stage[r][col];
+      p.attr_out[(size_t)sm.sidx[r] * LSG_NSIG + col] = v;
+      const uint32_t inc = sm.span[r][1].z;
+      if (p.inc_keys && inc != LSG_NONE && inc < p.n_incidents && !isnan(v))
+        atomicMax(&p.inc_keys[(size_t)inc * LSG_NSIG + col], f64_key(v));
+    }
+    __syncthreads();     // staging is reused by the next chunk
+  }
+  // counters: lanes -> warp (REDUX needs 32-bit pieces, so shuffle-add the 64-bit values) -> block -> one atomic
+  for (int o = 16; o; o >>= 1) {
+    w_matched += __shfl_xor_sync(0xffffffffu, w_matched, o);
+    w_low += __shfl_xor_sync(0xffffffffu, w_low, o);
+    w_drop += __shfl_xor_sync(0xffffffffu, w_drop, o);
+    w_cand += __shfl_xor_sync(0xffffffffu, w_cand, o);
+    w_kept += __shfl_xor_sync(0xffffffffu, w_kept, o);
   }
   if (lane == 0) {
     if (w_matched) atomicAdd(&sm.cnt[0], w_matched);
@@ -367,31 +618,59 @@ k_join_tiles(const __grid_constant__ JoinParams p) {
   if (tid < 5 && sm.cnt[tid]) atomicAdd(&p.counters[tid], sm.cnt[tid]);
 }
 
+// ---- spans whose own range exceeds a tile: one warp per span, straight from global memory ---------------
+__global__ void __launch_bounds__(JT_THREADS)
+k_join_big(const __grid_constant__ JoinParams p, const uint32_t *__restrict__ big_list, const unsigned int *__restrict__ big_count) {
+  __shared__ Cand s_list[JT_WARPS][JT_LIST];
+  __shared__ unsigned long long s_cnt[5];
+  const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < 5) s_cnt[tid] = 0;
+  __syncthreads();
+  unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
+  const unsigned n = *big_count;
+  const Cols g{p.ev.ts, p.ev.ident, p.ev.pid, p.ev.conn, p.ev.trsig, p.ev_perm, 0u};
+  for (unsigned i = blockIdx.x * JT_WARPS + warp; i < n; i += gridDim.x * JT_WARPS) {
+    const size_t q = big_list[i];
+    const size_t si = p.span_perm ? p.span_perm[q] : q;
+    const SpanRec s = load_span(p.spans + si);
+    process_span(p, g, s_list[warp], s, si, p.ranges[q], lane, w_matched, w_low, w_drop, w_cand, w_kept);
+  }
+  if (lane == 0) {
+    if (w_matched) atomicAdd(&s_cnt[0], w_matched);
+    if (w_low) atomicAdd(&s_cnt[1], w_low);
+    if (w_drop) atomicAdd(&s_cnt[2], w_drop);
+    if (w_cand) atomicAdd(&s_cnt[3], w_cand);
+    if (w_kept) atomicAdd(&s_cnt[4], w_kept);
+  }
+  __syncthreads();
+  if (tid < 5 && s_cnt[tid]) atomicAdd(&p.counters[tid], s_cnt[tid]);
+}
+
 }  // namespace
 
 int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   LSG_CUDA(ctx, cudaMemsetAsync(a.counters, 0, 8 * sizeof(uint64_t), ctx->stream));
   if (a.n_spans == 0) return 0;
   void *rv = nullptr;
-  LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * sizeof(uint2), &rv));
-  ProfScope ps(ctx, PK_JOIN);
+  LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * (sizeof(uint4) + sizeof(uint32_t)), &rv));
   const uint32_t n_live = (uint32_t)a.ev.n_live;
   {
+    ProfScope ps(ctx, PK_RANGES);
     size_t blocks = (a.n_spans + 255) / 256, cap = (size_t)ctx->sm_count * 8;
     if (blocks > cap) blocks = cap;
     if (a.ev.key.bits <= 31)
       k_span_ranges<uint32_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint32_t *)a.ev.keys,
                                                                       n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
-                                                                      a.window_ns, (uint2 *)rv, (unsigned long long *)a.counters);
+                                                                      a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
     else
       k_span_ranges<uint64_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint64_t *)a.ev.keys,
                                                                       n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
-                                                                      a.window_ns, (uint2 *)rv, (unsigned long long *)a.counters);
+                                                                      a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
     LSG_LAUNCH_CHECK(ctx);
   }
   JoinParams p;
   p.spans = a.spans; p.span_perm = a.span_perm; p.n_spans = a.n_spans;
-  p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint2 *)rv;
+  p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv;
   p.idents = a.idents; p.n_idents = (uint32_t)a.n_idents;
   p.window_ns = a.window_ns; p.threshold = a.threshold; p.fanout = a.fanout;
   p.attr_base = a.attr_base; p.cand_event = a.cand_event; p.cand_tier = a.cand_tier; p.attr_out = a.attr_out;
@@ -399,15 +678,29 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   p.counters = (unsigned long long *)a.counters;
   p.inc_keys = a.inc_keys; p.n_incidents = a.n_incidents;
   const size_t n_chunks = (a.n_spans + JT_CH - 1) / JT_CH;
-  size_t blocks = n_chunks, cap = (size_t)ctx->sm_count * 4;
-  if (blocks > cap) blocks = cap;
-  const size_t smem = sizeof(JoinSmem);
-  if (a.fanout <= 3) {
-    LSG_CUDA(ctx, cudaFuncSetAttribute(k_join_tiles<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_join_tiles<3><<<(unsigned)blocks, JT_THREADS, smem, ctx->stream>>>(p);
-  } else {
-    LSG_CUDA(ctx, cudaFuncSetAttribute(k_join_tiles<LSG_MAX_FANOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_join_tiles<LSG_MAX_FANOUT><<<(unsigned)blocks, JT_THREADS, smem, ctx->stream>>>(p);
+  const size_t smem = sizeof(TileSmem);
+  // spans that do not fit a tile are listed for k_join_big; the list lives behind the ranges
+  uint32_t *big_list = (uint32_t *)((char *)rv + a.n_spans * sizeof(uint4));
+  unsigned int *big_count = (unsigned int *)(a.counters + 6);
+  ProfScope ps(ctx, PK_JOIN);
+  // persistent grid: exactly as many CTAs as are resident at once (SM count x occupancy), each striding over chunks
+  auto launch = [&](auto kernel) -> int {
+    LSG_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    LSG_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, JT_THREADS, smem));
+    if (occ < 1) occ = 1;
+    size_t blocks = n_chunks, cap = (size_t)ctx->sm_count * occ;
+    if (blocks > cap) blocks = cap;
+    kernel<<<(unsigned)blocks, JT_THREADS, smem, ctx->stream>>>(p, big_list, big_count);
+    return 0;
+  };
+  if (a.fanout <= 3) LSG_TRY(launch(k_join_tiles<3>));
+  else LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT>));
+  LSG_LAUNCH_CHECK(ctx);
+  {
+    size_t blocks = (a.n_spans + JT_WARPS - 1) / JT_WARPS, cap = (size_t)ctx->sm_count * 4;
+    if (blocks > cap) blocks = cap;
+    k_join_big<<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
   }
   LSG_LAUNCH_CHECK(ctx);
   return 0;

@@ -435,8 +435,8 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
   void *ka, *kb, *ia, *ib;
   LSG_TRY(lsg_ws(ctx, WS_KEYS_A, n * (k32 ? 4 : 8), &ka));
   LSG_TRY(lsg_ws(ctx, WS_KEYS_B, n * (k32 ? 4 : 8), &kb));
-  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4, &ia));
-  LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4, &ib));
+  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &ia));   // + padding: the join's bulk copies run up to 3 entries past n
+  LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4 + 64, &ib));
   uint32_t *perm = nullptr;
   if (k32) {
     {
