@@ -110,6 +110,9 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
         search(W, 0, n_live, &r.x, &r.y);
         const int64_t Wi = W < 500 * kMs ? W : 500 * kMs;          // tiers 2-4: dns.go:62-73
         search(Wi, r.x, r.y, &r.z, &r.w);                           // inside the outer range: a short search
+        // a span whose own time lies outside the events' time range was clamped into the key space: its inner
+        // range is still a superset, but the tile kernel's 32-bit time deltas are not safe for it -> k_join_big
+        if (tc != s.ts) r.z = r.w = 0xffffffffu;
       }
     }
     ranges[q] = r;
@@ -190,11 +193,13 @@ __device__ __forceinline__ int select_best(const Cand *list, const int n, const 
 
 // One span, one warp: scan, select, write.  Counters go to the caller's per-lane accumulators.
 __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, Cand *list, const SpanRec s, const size_t si,
-                                             const uint4 rg, const unsigned lane, unsigned long long &w_matched,
+                                             const uint4 rg_in, const unsigned lane, unsigned long long &w_matched,
                                              unsigned long long &w_low, unsigned long long &w_drop, unsigned long long &w_cand,
                                              unsigned long long &w_kept) {
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
   const unsigned lt_mask = (1u << lane) - 1u;
+  uint4 rg = rg_in;
+  if (rg.z == 0xffffffffu) { rg.z = rg.x; rg.w = rg.y; }   // no inner range recorded: the outer one is a superset
   const uint64_t W = (uint64_t)p.window_ns;
   unsigned n_cand = 0, n_match = 0, n_low = 0;
   int n_list = 0;   // warp-uniform
@@ -334,16 +339,21 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
   return s;
 }
 
-// ---- the tile kernel: two threads per span -------------------------------------------------------------
-// A warp that serves one span pays a vote or ballot for every rare event.  Here each span gets two threads
-// (lanes 2k, 2k+1): each scans half of the span's outer range for trace-id hits (128-bit loads of the
-// trace|signal column) and half of its inner range with the full tier 2-4 decision, out of the shared tile,
-// with plain per-thread code.  Hits are only noted — two bytes (tier, tile offset) in a per-thread list —
-// and ordered afterwards in registers, when every lane of the warp is doing the same thing; the two
-// halves are merged with shuffles.  Attribute rows go through a shared staging buffer so that the 96-byte
-// rows leave as coalesced stores.
+// ---- the tile kernel -------------------------------------------------------------------------------------
+// A warp that serves one span pays a vote or ballot for every rare event, and scanning a span's whole outer
+// window for trace-id matches repeats, for every span, work that is an equality join.  So per tile:
+//   tier 1 (dns.go:58-60)  the chunk's span trace ids sit in a 256-slot shared-memory hash; every event of the
+//                          tile is looked at ONCE by one thread and probes it.  A same-trace pair is a match iff
+//                          |dt| <= W, and such an event is inside the span's range, hence inside the tile.
+//   tiers 2-4 (dns.go:61-73) need |dt| <= 500 ms: two threads per span (lanes 2k, 2k+1) each walk half of the
+//                          span's inner range with plain per-thread code; time deltas fit 32 bits there.
+// A match is only noted — two bytes (tier, tile offset) in the span's list — and the lists are ordered
+// afterwards in registers, when every lane is doing the same thing.  A span whose list overflows (or whose range
+// does not fit a tile) is left to k_join_big.
 constexpr int TM_CAP = 1920;    // events per tile
-constexpr int TM_LIST = 16;     // noted hits per thread before they are condensed to the best `fanout`
+constexpr int TM_LIST = 48;     // noted candidates per span
+constexpr int TM_HASH = 256;    // hash slots for the chunk's span trace ids (<= 128 keys)
+constexpr uint16_t TM_END = 0xffffu;
 
 template <int F>
 struct TopF {
@@ -376,26 +386,19 @@ struct TileSmem {
   uint4 span[JT_CH][2];
   uint4 rng[JT_CH];
   uint32_t sidx[JT_CH];
-  uint16_t note[TM_LIST][JT_THREADS];   // entry-major: consecutive lanes, consecutive halfwords
-  double stage[JT_CH][LSG_NSIG];        // attribute rows of the chunk
+  uint16_t note[TM_LIST][JT_CH];    // entry-major: consecutive spans, consecutive halfwords
+  uint32_t n_note[JT_CH];           // candidates noted per span (may exceed TM_LIST: then the span is redone by k_join_big)
+  uint32_t n_tr[JT_CH];             // trace-id matches per span (tier 1), candidates or not
+  uint32_t hkey[TM_HASH];           // trace id, 0 = empty
+  uint16_t hhead[TM_HASH];          // first span of the chain for that trace id
+  uint16_t hnext[JT_CH];            // next span with the same trace id
   unsigned long long cnt[5];
   uint64_t bar;
 };
 
-// order the noted hits of one thread: exact |dt| from the tile, input index from the permutation
-template <int F>
-__device__ __forceinline__ void order_notes(const TileSmem &sm, const JoinParams &p, const unsigned tid, const int n,
-                                            const int64_t s_ts, const uint32_t base, TopF<F> &top) {
-#pragma unroll 4
-  for (int i = 0; i < n; ++i) {
-    const uint32_t e = sm.note[i][tid];
-    const uint32_t o = e & 0xfffu, tier = e >> 12;
-    const uint64_t adt = lsg_absdiff(s_ts, sm.ts[o]);
-    top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[base + o], base + o);
-  }
-}
+__device__ __forceinline__ uint32_t trace_slot(uint32_t tr) { return (tr * 2654435761u) >> 24; }   // 8 bits
 
-template <int F>
+template <int F, bool T32>
 __global__ void __launch_bounds__(JT_THREADS, 3)
 k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -410,11 +413,13 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
   const size_t n_chunks = (p.n_spans + JT_CH - 1) / JT_CH;
   const uint64_t W = (uint64_t)p.window_ns;
   const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
+  // confidence falls with the tier (1.0, 0.9, 0.8, 0.65), so "confidence >= threshold" is "tier <= cut"
+  const int cut = (1.0 >= p.threshold) + (0.9 >= p.threshold) + (0.8 >= p.threshold) + (0.65 >= p.threshold);
 
   for (size_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
     const size_t q0 = chunk * JT_CH;
     const int nq = (int)min((size_t)JT_CH, p.n_spans - q0);
-    // stage the chunk's spans: input index, ranges, record (two 16-byte halves per span), attribute rows
+    // ---- stage the chunk's spans: input index, ranges, record (two 16-byte halves per span); clear the hash
     if ((int)tid < nq) {
       sm.rng[tid] = p.ranges[q0 + tid];
       sm.sidx[tid] = p.span_perm ? p.span_perm[q0 + tid] : (uint32_t)(q0 + tid);
@@ -426,10 +431,28 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         sm.span[k][half] = ld_nc_v4(reinterpret_cast<const uint4 *>(p.spans + si) + half);
       }
     }
+    sm.hkey[tid] = 0;            // JT_THREADS == TM_HASH
+    sm.hhead[tid] = TM_END;
     __syncthreads();
-    for (int i = tid; i < nq * LSG_NSIG; i += JT_THREADS) {
-      const int r = i / LSG_NSIG, col = i - r * LSG_NSIG;
-      sm.stage[r][col] = p.attr_base ? p.attr_base[(size_t)sm.sidx[r] * LSG_NSIG + col] : nan;
+    // ---- hash of the chunk's non-zero span trace ids; spans that share an id are chained
+    if ((int)tid < nq) {
+      const uint32_t tr = sm.span[tid][1].y;
+      if (tr != 0) {
+        uint32_t slot = trace_slot(tr);
+        for (;;) {
+          const uint32_t prev = atomicCAS(&sm.hkey[slot], 0u, tr);
+          if (prev == 0u || prev == tr) break;
+          slot = (slot + 1) & (TM_HASH - 1);
+        }
+        // push front (16-bit exchange through the containing word is not available: serialise per slot with a CAS loop)
+        unsigned short *hp = &sm.hhead[slot];
+        unsigned short old = *hp, assumed;
+        do {
+          assumed = old;
+          sm.hnext[tid] = assumed;
+          old = atomicCAS(hp, assumed, (unsigned short)tid);
+        } while (old != assumed);
+      }
     }
     int i0 = 0;
     while (i0 < nq) {
@@ -455,124 +478,156 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           bulk_g2s(sm.pid, p.ev.pid + A, count * 4u, &sm.bar);
           bulk_g2s(sm.conn, p.ev.conn + A, count * 4u, &sm.bar);
         }
+      }
+      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; }
+      if (count) {
         mbar_wait(&sm.bar, phase);
         phase ^= 1;
       }
-      // ---- scan: thread (2k + h) takes half h of span k's ranges; 128 spans per round of the block
-      for (int kb = i0; kb < i1; kb += JT_THREADS / 2) {
-        const int k = kb + (int)(tid >> 1);
-        const unsigned h = tid & 1;
-        const bool live = k < i1;
-        unsigned n_cand = 0, n_match = 0, n_low = 0;
-        int n_note = 0;
-        SpanRec s;
-        s.ts = 0; s.ident = 0; s.pid = 0; s.conn = 0; s.trace = 0; s.incident = LSG_NONE;
-        TopF<F> top;
-        top.init();
-        if (live) {
-          s = span_from_halves(sm.span[k][0], sm.span[k][1]);
+      __syncthreads();
+      // ---- tier 1: every event of the tile probes the hash once
+      const uint32_t live_end = min(count, sm.rng[i1 - 1].y - A);
+      for (uint32_t o = tid; o < live_end; o += JT_THREADS) {
+        const uint32_t tr = sm.trsig[o] >> 4;
+        if (tr == 0) continue;
+        uint32_t slot = trace_slot(tr);
+        uint32_t key;
+        while ((key = sm.hkey[slot]) != 0u && key != tr) slot = (slot + 1) & (TM_HASH - 1);
+        if (key != tr) continue;
+        const int64_t e_ts = sm.ts[o];
+        for (uint32_t k = sm.hhead[slot]; k != TM_END; k = sm.hnext[k]) {
+          if ((int)k < i0 || (int)k >= i1) continue;                 // that span belongs to another tile of the chunk
           const uint4 rg = sm.rng[k];
-          // note a hit; when the list is full, condense it to the entries that can still win
-          auto note = [&](const uint32_t tier, const uint32_t o) {
-            if (n_note == TM_LIST) {
-              TopF<F> t2;
-              t2.init();
-              order_notes<F>(sm, p, tid, n_note, s.ts, A, t2);
-              n_note = 0;
-#pragma unroll
-              for (int r = 0; r < F; ++r)
-                if (t2.idx[r] != 0xffffffffu && r < p.fanout)
-                  sm.note[n_note++][tid] = (uint16_t)(((uint32_t)(t2.k1[r] >> 56) << 12) | (t2.pos[r] - A));
-            }
-            sm.note[n_note++][tid] = (uint16_t)((tier << 12) | o);
-            n_cand++;
-          };
-          if (rg.x < rg.y) {
-            // tier 1 (dns.go:58-60): trace-id equality anywhere in the outer window; 4 events per 128-bit load
-            if (s.trace != 0) {
-              const uint32_t xo = rg.x - A, yo = rg.y - A;
-              const uint32_t mid = (xo + ((yo - xo) >> 1) + 3u) & ~3u;      // both halves start 16-byte aligned
-              const uint32_t beg = h ? min(mid, yo) : xo, end = h ? yo : min(mid, yo);
-              for (uint32_t v = beg & ~3u; v < end; v += 4) {
-                const uint4 q = *reinterpret_cast<const uint4 *>(sm.trsig + v);
-                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const uint32_t o = v + e;
-                  if ((w[e] >> 4) == s.trace && o >= beg && o < end) {
-                    const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
-                    if (adt <= W) {                                  // outer window, dns.go:54-56
-                      n_match++;
-                      if (1.0 < p.threshold) n_low++; else note(LSG_TIER_TRACE, o);
-                    }
-                  }
-                }
-              }
-            }
-            // tiers 2-4 (dns.go:61-73) need |dt| <= 500 ms: the inner range; trace-id matches were taken above
-            if (rg.z < rg.w) {
-              const lsg_ident sid = load_ident(p.idents, s.ident);
-              const uint32_t zo = rg.z - A, wo = rg.w - A;
-              const uint32_t mid = zo + ((wo - zo) >> 1);
-              const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
-              for (uint32_t o = beg; o < end; ++o) {
-                const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
-                if (adt > Wi) continue;
-                const uint32_t trsig = sm.trsig[o];
-                if (s.trace != 0 && s.trace == (trsig >> 4)) continue;
-                const uint32_t e_ident = sm.ident[o];
-                lsg_ident eid = sid;
-                if (e_ident != s.ident) eid = load_ident(p.idents, e_ident);
-                const int tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, sm.pid[o], sm.conn[o], eid);
-                if (tier == 0) continue;                             // Unmatched: counted analytically by the caller
-                n_match++;
-                if (lsg_tier_conf(tier) < p.threshold) n_low++;      // correlator.go:83-86
-                else note((uint32_t)tier, o);
-              }
-            }
+          if (o + A < rg.x || o + A >= rg.y) continue;                // outside its range: cannot be within the window
+          const int64_t s_ts = (int64_t)(((uint64_t)sm.span[k][0].y << 32) | sm.span[k][0].x);
+          if (lsg_absdiff(s_ts, e_ts) > W) continue;                  // outer window, dns.go:54-56
+          atomicAdd(&sm.n_tr[k], 1u);
+          if (cut >= 1) {
+            const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+            if (at < TM_LIST) sm.note[at][k] = (uint16_t)((LSG_TIER_TRACE << 12) | o);
           }
         }
-        // ---- order: every lane sorts its own notes, then the odd lane hands its best F to the even lane
-        order_notes<F>(sm, p, tid, n_note, s.ts, A, top);
-#pragma unroll
-        for (int r = 0; r < F; ++r) {
-          const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
-          const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
-          const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
-          if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
+      }
+      // ---- tiers 2-4: thread (2k + h) walks half h of span k's inner range
+      const int k = i0 + (int)(tid >> 1);
+      const unsigned h = tid & 1;
+      const bool live = k < i1;
+      unsigned n_match = 0, n_low = 0;
+      SpanRec s;
+      s.ts = 0; s.ident = 0; s.pid = 0; s.conn = 0; s.trace = 0; s.incident = LSG_NONE;
+      if (live) {
+        s = span_from_halves(sm.span[k][0], sm.span[k][1]);
+        const uint4 rg = sm.rng[k];
+        if (rg.z < rg.w && rg.z != 0xffffffffu) {
+          const lsg_ident sid = load_ident(p.idents, s.ident);
+          const bool pod_ok = sid.pod != 0, svcnode_ok = sid.service != 0 && sid.node != 0;
+          const uint32_t zo = rg.z - A, wo = rg.w - A;
+          const uint32_t mid = zo + ((wo - zo) >> 1);
+          const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
+          const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
+          const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);   // little endian: low words at even indices
+          for (uint32_t o = beg; o < end; ++o) {
+            uint64_t adt;
+            if (T32) {   // |dt| < 2^31 ns for every event of an inner range: 32-bit arithmetic is exact
+              const int32_t d = (int32_t)(ts_lo[2 * o] - s_lo);
+              adt = (uint32_t)(d < 0 ? -d : d);
+            } else {
+              adt = lsg_absdiff(s.ts, sm.ts[o]);
+            }
+            if (adt > Wi) continue;
+            if (s.trace != 0 && s.trace == (sm.trsig[o] >> 4)) continue;        // tier 1, taken by the hash pass
+            const uint32_t e_ident = sm.ident[o];
+            bool same_pod = pod_ok, same_sn = svcnode_ok;
+            if (e_ident != s.ident) {
+              const lsg_ident eid = load_ident(p.idents, e_ident);
+              same_pod = pod_ok && sid.pod == eid.pod;
+              same_sn = svcnode_ok && sid.service == eid.service && sid.node == eid.node;
+            }
+            int tier = 0;
+            if (same_pod && s.pid != 0 && s.pid == sm.pid[o] && adt <= (uint64_t)(100 * kMs)) tier = LSG_TIER_POD_PID;          // dns.go:61-64
+            else if (same_pod && s.conn != 0 && s.conn == sm.conn[o] && adt <= (uint64_t)(250 * kMs)) tier = LSG_TIER_POD_CONN;  // dns.go:65-68
+            else if (same_sn) tier = LSG_TIER_SVC_NODE;                        // dns.go:69-73 (adt <= Wi <= 500 ms holds)
+            if (tier == 0) continue;                                           // Unmatched: counted analytically by the caller
+            n_match++;
+            if (tier > cut) { n_low++; continue; }                             // correlator.go:83-86
+            const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+            if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+          }
         }
-        n_cand += __shfl_down_sync(0xffffffffu, n_cand, 1);
-        n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
-        n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
-        // ---- write: the even lane owns the span
-        int kept = 0;
-        if (live && !h) {
-          const size_t si = sm.sidx[k];
-          double *row = sm.stage[k];
-          double vals[F];
+      }
+      __syncthreads();   // every note of the tile is in place
+      // ---- order: lane h takes the notes of parity h, then the odd lane hands its best F to the even lane
+      TopF<F> top;
+      top.init();
+      uint32_t n_cand = 0;
+      bool redo = false;
+      if (live) {
+        n_cand = sm.n_note[k];
+        redo = n_cand > (uint32_t)TM_LIST || sm.rng[k].z == 0xffffffffu;
+        if (!redo) {
+#pragma unroll 2
+          for (uint32_t i = h; i < n_cand; i += 2) {
+            const uint32_t e = sm.note[i][k];
+            const uint32_t o = e & 0xfffu, tier = e >> 12;
+            const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
+            top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[A + o], A + o);
+          }
+        }
+      }
 #pragma unroll
-          for (int r = 0; r < F; ++r) vals[r] = (r < p.fanout && top.idx[r] != 0xffffffffu) ? p.ev.val[top.pos[r]] : 0.0;
+      for (int r = 0; r < F; ++r) {
+        const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
+        const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
+        const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
+        if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
+      }
+      n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
+      n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
+      // ---- write: the even lane owns the span
+      if (live && !h) {
+        if (redo) {
+          big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q0 + k);   // more candidates than the list holds
+        } else {
+          const size_t si = sm.sidx[k];
+          const uint32_t n_tr = sm.n_tr[k];
+          n_match += n_tr;
+          if (cut < 1) n_low += n_tr;
+          double vals[F];
+          unsigned sigs[F];
+          int kept = 0;
 #pragma unroll
           for (int r = 0; r < F; ++r) {
+            const bool has = r < p.fanout && top.idx[r] != 0xffffffffu;
+            vals[r] = has ? p.ev.val[top.pos[r]] : 0.0;
+            sigs[r] = has ? (sm.trsig[top.pos[r] - A] & 15u) : 0xffu;
+            kept += has;
             if (r < p.fanout) {
-              const bool has = top.idx[r] != 0xffffffffu;
               p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
               p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
-              if (has) {
-                kept++;
-                const unsigned sig = sm.trsig[top.pos[r] - A] & 15u;                        // per-attribute max, correlator.go:106-112
-                const double cur = row[sig];
-                if (isnan(cur) || vals[r] > cur) row[sig] = vals[r];
-              }
             }
+          }
+          // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
+          double v0 = nan, v3 = nan, v4 = nan;
+#pragma unroll
+          for (int col = 0; col < LSG_NSIG; ++col) {
+            double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
+#pragma unroll
+            for (int r = 0; r < F; ++r)
+              if (sigs[r] == (unsigned)col && (isnan(v) || vals[r] > v)) v = vals[r];
+            p.attr_out[si * LSG_NSIG + col] = v;
+            if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(v))
+              atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
+            if (col == 0) v0 = v;
+            if (col == 3) v3 = v;
+            if (col == 4) v4 = v;
           }
           // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
           p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
           if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
             double total = 0.0;
-            if (!isnan(row[0])) total += row[0];
-            if (!isnan(row[3])) total += row[3];
-            if (!isnan(row[4])) total += row[4];
+            if (!isnan(v0)) total += v0;
+            if (!isnan(v3)) total += v3;
+            if (!isnan(v4)) total += v4;
             p.retrieval_out[si] = total;
           }
           if (p.n_cand_out) p.n_cand_out[si] = n_cand;
@@ -580,26 +635,15 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           w_low += n_low;
           w_cand += n_cand;
           w_kept += kept;
-          if (n_cand > (unsigned)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
+          if (n_cand > (uint32_t)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
         }
       }
       __syncthreads();   // every thread is done with the tile before the next bulk copy overwrites it
       i0 = i1;
     }
-    // ---- the chunk's attribute rows leave as coalesced 96-byte rows; per-incident maxima (A7) ride along
-    for (int i = tid; i < nq * LSG_NSIG; i += JT_THREADS) {
-      const int r = i / LSG_NSIG, col = i - r * LSG_NSIG;
-      const uint4 rg = sm.rng[r];
-      if (rg.y - (rg.x & ~3u) > (uint32_t)(TM_CAP - 4)) continue;        // left to k_join_big
-      const double v = sm.stage[r][col];
-      p.attr_out[(size_t)sm.sidx[r] * LSG_NSIG + col] = v;
-      const uint32_t inc = sm.span[r][1].z;
-      if (p.inc_keys && inc != LSG_NONE && inc < p.n_incidents && !isnan(v))
-        atomicMax(&p.inc_keys[(size_t)inc * LSG_NSIG + col], f64_key(v));
-    }
-    __syncthreads();     // staging is reused by the next chunk
+    __syncthreads();     // the span staging and the hash are reused by the next chunk
   }
-  // counters: lanes -> warp (REDUX needs 32-bit pieces, so shuffle-add the 64-bit values) -> block -> one atomic
+  // counters: lanes -> warp -> block -> one atomic
   for (int o = 16; o; o >>= 1) {
     w_matched += __shfl_xor_sync(0xffffffffu, w_matched, o);
     w_low += __shfl_xor_sync(0xffffffffu, w_low, o);
@@ -694,8 +738,14 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
     kernel<<<(unsigned)blocks, JT_THREADS, smem, ctx->stream>>>(p, big_list, big_count);
     return 0;
   };
-  if (a.fanout <= 3) LSG_TRY(launch(k_join_tiles<3>));
-  else LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT>));
+  // inner ranges reach at most min(W, 500 ms) + two time quanta from the span: 32-bit deltas when that is < 2^31 ns
+  const int64_t wi = a.window_ns < 500 * kMs ? a.window_ns : 500 * kMs;
+  const bool t32 = a.ev.key.shift < 29 && wi + ((int64_t)2 << a.ev.key.shift) < ((int64_t)1 << 31);
+  if (a.fanout <= 3) {
+    if (t32) LSG_TRY(launch(k_join_tiles<3, true>)); else LSG_TRY(launch(k_join_tiles<3, false>));
+  } else {
+    if (t32) LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT, true>)); else LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT, false>));
+  }
   LSG_LAUNCH_CHECK(ctx);
   {
     size_t blocks = (a.n_spans + JT_WARPS - 1) / JT_WARPS, cap = (size_t)ctx->sm_count * 4;
