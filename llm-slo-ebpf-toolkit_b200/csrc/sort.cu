@@ -116,24 +116,50 @@ k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__res
 }
 
 // ---- one radix pass ------------------------------------------------------------------------------
+// lanes of the warp whose 8-bit digit equals this lane's: eight ballots instead of match.any, which is
+// issued through the (slow, shared) MIO queue on sm_100 and throttled both radix kernels
+__device__ __forceinline__ unsigned peers_of_digit(const unsigned d) {
+  unsigned peers = 0xffffffffu;
+#pragma unroll
+  for (int b = 0; b < RADIX_BITS; ++b) {
+    const bool bit = (d >> b) & 1u;
+    const unsigned bal = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? bal : ~bal;
+  }
+  return peers;
+}
+
 template <typename KeyT>
 __global__ void __launch_bounds__(SORT_BLOCK)
 k_radix_hist(const KeyT *__restrict__ keys, size_t n, int shift, uint32_t *__restrict__ tile_hist, uint32_t n_tiles) {
-  __shared__ uint32_t s_hist[RADIX];
-  for (int i = threadIdx.x; i < RADIX; i += SORT_BLOCK) s_hist[i] = 0;
+  __shared__ uint32_t s_hist[SORT_NW][RADIX];   // one counter row per warp: leaders update without atomics
+  for (int i = threadIdx.x; i < SORT_NW * RADIX; i += SORT_BLOCK) (&s_hist[0][0])[i] = 0;
   __syncthreads();
   const size_t base = (size_t)blockIdx.x * SORT_TILE;
-  const unsigned lane = threadIdx.x & 31;
-#pragma unroll 4
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t *mine = s_hist[warp];
+  KeyT k[SORT_IPT];
+#pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
-    size_t pos = base + (size_t)i * SORT_BLOCK + threadIdx.x;
-    bool valid = pos < n;
-    unsigned d = valid ? (unsigned)((keys[pos] >> shift) & (RADIX - 1)) : 0xffffffffu;
-    unsigned m = __match_any_sync(0xffffffffu, d);
-    if (valid && lane == (unsigned)(__ffs(m) - 1)) atomicAdd(&s_hist[d], __popc(m));
+    const size_t pos = base + (size_t)i * SORT_BLOCK + threadIdx.x;
+    k[i] = pos < n ? keys[pos] : (KeyT)0;
+  }
+#pragma unroll
+  for (int i = 0; i < SORT_IPT; ++i) {
+    const size_t pos = base + (size_t)i * SORT_BLOCK + threadIdx.x;
+    const bool valid = pos < n;
+    const unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
+    const unsigned peers = peers_of_digit(d) & __ballot_sync(0xffffffffu, valid);
+    if (valid && lane == (unsigned)(__ffs(peers) - 1)) mine[d] += __popc(peers);
+    __syncwarp();
   }
   __syncthreads();
-  for (int d = threadIdx.x; d < RADIX; d += SORT_BLOCK) tile_hist[(size_t)d * n_tiles + blockIdx.x] = s_hist[d];
+  for (int d = threadIdx.x; d < RADIX; d += SORT_BLOCK) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_NW; ++w) t += s_hist[w][d];
+    tile_hist[(size_t)d * n_tiles + blockIdx.x] = t;
+  }
 }
 
 // exclusive scan of each digit's row over the tiles (in place); one CTA per digit
@@ -188,7 +214,7 @@ __global__ void __launch_bounds__(RADIX) k_radix_scan_digits(const uint32_t *__r
 }
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_BLOCK)
+__global__ void __launch_bounds__(SORT_BLOCK, 2)
 k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ idx_in, KeyT *__restrict__ keys_out,
                 uint32_t *__restrict__ idx_out, size_t n, int shift, const uint32_t *__restrict__ tile_off,
                 const uint32_t *__restrict__ digit_base, uint32_t n_tiles) {
@@ -208,15 +234,12 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
 
   // warp-striped load: warp w owns tile slots [w*32*IPT, (w+1)*32*IPT), item i of lane l is slot i*32+l
   KeyT k[SORT_IPT];
-  uint32_t v[SORT_IPT];
-  uint32_t rank[SORT_IPT];
+  uint16_t rank[SORT_IPT];
   const size_t wbase = base + (size_t)warp * 32 * SORT_IPT;
 #pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
     size_t pos = wbase + (size_t)i * 32 + lane;
-    bool valid = pos < n;
-    k[i] = valid ? keys_in[pos] : (KeyT)~(KeyT)0;   // padding sorts behind every real key of the tile (stable)
-    v[i] = valid ? (idx_in ? idx_in[pos] : (uint32_t)pos) : 0u;
+    k[i] = pos < n ? keys_in[pos] : (KeyT)~(KeyT)0;   // padding sorts behind every real key of the tile (stable)
   }
   // stable rank of each item among the items of its warp with the same digit
   uint32_t *my_cnt = warp_cnt + warp * RADIX;
@@ -224,7 +247,7 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
 #pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
     unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
-    unsigned m = __match_any_sync(0xffffffffu, d);
+    unsigned m = peers_of_digit(d);
     int leader = __ffs(m) - 1;
     uint32_t old = 0;
     if ((int)lane == leader) {
@@ -232,7 +255,7 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
       my_cnt[d] = old + __popc(m);
     }
     old = __shfl_sync(0xffffffffu, old, leader);
-    rank[i] = old + __popc(m & lt_mask);
+    rank[i] = (uint16_t)(old + __popc(m & lt_mask));
     __syncwarp();
   }
   __syncthreads();
@@ -263,12 +286,15 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
     gbase[tid] = digit_base[tid] + tile_off[(size_t)tid * n_tiles + blockIdx.x] - excl;
   }
   __syncthreads();
+  // the payload (input index) is read only now, so that it never sits in registers during the ranking
 #pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
+    const size_t pos = wbase + (size_t)i * 32 + lane;
+    const uint32_t v = pos < n ? (idx_in ? idx_in[pos] : (uint32_t)pos) : 0u;
     unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
     uint32_t lp = bin_off[d] + my_cnt[d] + rank[i];
     s_keys[lp] = k[i];
-    s_idx[lp] = v[i];
+    s_idx[lp] = v;
   }
   __syncthreads();
   // tile is now in digit order in shared memory: runs of equal digits go to consecutive global slots
