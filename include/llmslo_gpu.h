@@ -15,6 +15,8 @@
  *     functions take DEVICE pointers on the context's device and leave results on the device.
  *     Every call returns after its work on the context's stream has completed, except `_dev`
  *     calls documented as asynchronous.
+ *   - device record arrays (lsg_event, lsg_span) passed to `_dev` functions must be 32-byte aligned (they are
+ *     read with 256-bit loads); cudaMalloc and framework allocators give at least that.
  *   - a context is bound to one device and one stream and is NOT thread-safe.
  *   - there is no CPU fallback: without a usable CUDA device lsg_create fails.
  *

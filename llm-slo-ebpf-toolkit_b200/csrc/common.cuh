@@ -181,13 +181,31 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void *p) {
 __device__ __forceinline__ uint4 ld_v4(const void *p) { return *reinterpret_cast<const uint4 *>(p); }
 __device__ __forceinline__ void st_v4(void *p, uint4 v) { *reinterpret_cast<uint4 *>(p) = v; }
 
+// 256-bit loads/stores (sm_100: LDG.E.256 / STG.E.256): one request per 32-byte record.  Needs 32-byte alignment,
+// which every record array has (cudaMalloc / torch allocations; documented in the header for caller buffers).
+struct U8 { uint4 a, b; };
+__device__ __forceinline__ U8 ld_nc_v8(const void *p) {
+  unsigned long long x, y, z, w;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(x), "=l"(y), "=l"(z), "=l"(w) : "l"(p));
+  U8 r;
+  r.a = make_uint4((uint32_t)x, (uint32_t)(x >> 32), (uint32_t)y, (uint32_t)(y >> 32));
+  r.b = make_uint4((uint32_t)z, (uint32_t)(z >> 32), (uint32_t)w, (uint32_t)(w >> 32));
+  return r;
+}
+__device__ __forceinline__ void st_v8(void *p, const U8 v) {
+  const unsigned long long x = ((unsigned long long)v.a.y << 32) | v.a.x, y = ((unsigned long long)v.a.w << 32) | v.a.z;
+  const unsigned long long z = ((unsigned long long)v.b.y << 32) | v.b.x, w = ((unsigned long long)v.b.w << 32) | v.b.z;
+  asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(p), "l"(x), "l"(y), "l"(z), "l"(w) : "memory");
+}
+
 struct EventRec {  // register image of an lsg_event
   int64_t ts;
   double value;
   uint32_t ident, pid, conn, trace_sig;
 };
 __device__ __forceinline__ EventRec load_event(const lsg_event *p) {
-  uint4 a = ld_v4(p), b = ld_v4(reinterpret_cast<const uint4 *>(p) + 1);
+  const U8 u = ld_nc_v8(p);
+  const uint4 a = u.a, b = u.b;
   EventRec r;
   r.ts = (int64_t)(((uint64_t)a.y << 32) | a.x);
   r.value = __longlong_as_double((long long)(((uint64_t)a.w << 32) | a.z));
@@ -199,7 +217,8 @@ struct SpanRec {
   uint32_t ident, pid, conn, trace, incident;
 };
 __device__ __forceinline__ SpanRec load_span(const lsg_span *p) {
-  uint4 a = ld_v4(p), b = ld_v4(reinterpret_cast<const uint4 *>(p) + 1);
+  const U8 u = ld_nc_v8(p);
+  const uint4 a = u.a, b = u.b;
   SpanRec r;
   r.ts = (int64_t)(((uint64_t)a.y << 32) | a.x);
   r.ident = a.z; r.pid = a.w; r.conn = b.x; r.trace = b.y; r.incident = b.z;

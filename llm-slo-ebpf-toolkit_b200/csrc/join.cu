@@ -424,12 +424,10 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       sm.rng[tid] = p.ranges[q0 + tid];
       sm.sidx[tid] = p.span_perm ? p.span_perm[q0 + tid] : (uint32_t)(q0 + tid);
     }
-    {
-      const int k = tid >> 1, half = tid & 1;
-      if (k < nq) {
-        const size_t si = p.span_perm ? p.span_perm[q0 + k] : q0 + k;
-        sm.span[k][half] = ld_nc_v4(reinterpret_cast<const uint4 *>(p.spans + si) + half);
-      }
+    if ((int)tid < nq) {
+      const U8 u = ld_nc_v8(p.spans + sm.sidx[tid]);
+      sm.span[tid][0] = u.a;
+      sm.span[tid][1] = u.b;
     }
     sm.hkey[tid] = 0;            // JT_THREADS == TM_HASH
     sm.hhead[tid] = TM_END;

@@ -310,16 +310,17 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
 __global__ void __launch_bounds__(256)
 k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n,
                 lsg_event *__restrict__ sorted) {
-  // two lanes per record: each moves one 16-byte half, so a warp writes 512 contiguous bytes
-  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // one 256-bit load and one 256-bit store per record; four records in flight per thread
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (; t < 2 * n; t += stride) {
-    size_t j = t >> 1;
-    unsigned half = (unsigned)(t & 1);
-    uint32_t src = perm[j];
-    uint4 val = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src) + half);
-    st_v4(reinterpret_cast<uint4 *>(sorted + j) + half, val);
+  size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; j + 3 * stride < n; j += 4 * stride) {
+    U8 r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) st_v8(sorted + j + u * stride, r[u]);
   }
+  for (; j < n; j += stride) st_v8(sorted + j, ld_nc_v8(events + perm[j]));
 }
 
 // the same gather into columns: what the join stages into shared memory (ts, ident, pid, conn, trace|signal) plus values
@@ -327,17 +328,25 @@ __global__ void __launch_bounds__(256)
 k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n, int64_t *__restrict__ ts,
                     double *__restrict__ val, uint32_t *__restrict__ ident, uint32_t *__restrict__ pid,
                     uint32_t *__restrict__ conn, uint32_t *__restrict__ trsig) {
-  for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (size_t)gridDim.x * blockDim.x) {
-    const uint32_t src = perm[j];
-    const uint4 a = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src));
-    const uint4 b = ld_nc_v4(reinterpret_cast<const uint4 *>(events + src) + 1);
-    ts[j] = (int64_t)(((uint64_t)a.y << 32) | a.x);
-    val[j] = __longlong_as_double((long long)(((uint64_t)a.w << 32) | a.z));
-    ident[j] = b.x;
-    pid[j] = b.y;
-    conn[j] = b.z;
-    trsig[j] = b.w;
+  auto put = [&](const size_t j, const U8 r) {
+    ts[j] = (int64_t)(((uint64_t)r.a.y << 32) | r.a.x);
+    val[j] = __longlong_as_double((long long)(((uint64_t)r.a.w << 32) | r.a.z));
+    ident[j] = r.b.x;
+    pid[j] = r.b.y;
+    conn[j] = r.b.z;
+    trsig[j] = r.b.w;
+  };
+  // one 256-bit load per record, four records in flight per thread; the column stores are coalesced
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; j + 3 * stride < n; j += 4 * stride) {
+    U8 r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) put(j + u * stride, r[u]);
   }
+  for (; j < n; j += stride) put(j, ld_nc_v8(events + perm[j]));
 }
 
 size_t scatter_smem(size_t key_bytes) {
@@ -502,7 +511,7 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
   }
   {
     ProfScope ps(ctx, PK_GATHER);
-    k_gather_events<<<grid_for(ctx, 2 * n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, sorted_out);
+    k_gather_events<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, sorted_out);
     LSG_LAUNCH_CHECK(ctx);
   }
   out->rec = sorted_out;

@@ -9,8 +9,7 @@ __global__ void __launch_bounds__(256) k_synth_spans(const __grid_constant__ lsg
     uint4 a, b;
     a.x = (uint32_t)(uint64_t)s.ts_ns; a.y = (uint32_t)((uint64_t)s.ts_ns >> 32); a.z = s.ident; a.w = s.pid;
     b.x = s.conn; b.y = s.trace; b.z = s.incident; b.w = 0;
-    st_v4(reinterpret_cast<uint4 *>(out + i), a);
-    st_v4(reinterpret_cast<uint4 *>(out + i) + 1, b);
+    st_v8(out + i, U8{a, b});
   }
 }
 __global__ void __launch_bounds__(256) k_synth_events(const __grid_constant__ lsg_synth_cfg c, lsg_event *out) {
@@ -20,8 +19,7 @@ __global__ void __launch_bounds__(256) k_synth_events(const __grid_constant__ ls
     const uint64_t vb = (uint64_t)__double_as_longlong(e.value);
     a.x = (uint32_t)(uint64_t)e.ts_ns; a.y = (uint32_t)((uint64_t)e.ts_ns >> 32); a.z = (uint32_t)vb; a.w = (uint32_t)(vb >> 32);
     b.x = e.ident; b.y = e.pid; b.z = e.conn; b.w = e.trace_sig;
-    st_v4(reinterpret_cast<uint4 *>(out + j), a);
-    st_v4(reinterpret_cast<uint4 *>(out + j) + 1, b);
+    st_v8(out + j, U8{a, b});
   }
 }
 __global__ void __launch_bounds__(256)
