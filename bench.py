@@ -184,6 +184,7 @@ def main():
 
     import llm_slo_ebpf_toolkit_b200 as pkg
     from llm_slo_ebpf_toolkit_b200 import _abi as A
+    from llm_slo_ebpf_toolkit_b200 import sharding
     from llm_slo_ebpf_toolkit_b200.device import DeviceWorkload
 
     rank = int(os.environ.get("RANK", "0"))
@@ -210,8 +211,7 @@ def main():
 
         def step():
             wl.step()
-            if world > 1:   # the only exchange of the path: sum of the confusion matrix / counter block
-                dist.all_reduce(wl.counters, op=dist.ReduceOp.SUM)
+            sharding.allreduce_counters(wl.counters)   # the only exchange of the path: sum of the counter block (N > 1)
 
         for _ in range(args.warmup):
             step()
