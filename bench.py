@@ -173,6 +173,7 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer measurement (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer measurement (C3 needs 37 GB of pinned memory)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -239,55 +240,64 @@ def main():
         ms_max = float(t.item())
         counters = wl.read_counters()
 
-        # ---- e2e: host (pinned) buffers through lsg_pipeline ----------------------------------------
-        e2e_steps = args.e2e_steps or min(args.steps, 10)
-        f = 3
-        host = {}
 
-        def pinned(nbytes):
-            return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, pin_memory=True)
+    def measure_e2e():
+        """host (pinned) buffers through lsg_pipeline: H2D of every record and D2H of every result inside the timed region"""
+        with torch.cuda.stream(stream):
+            e2e_steps = args.e2e_steps or min(args.steps, 10)
+            f = 3
+            host = {}
 
-        for name in ("events", "spans", "idents", "inc_actual", "inc_expected", "inc_expected_n"):
-            src = getattr(wl, name)
-            buf = pinned(src.numel() * src.element_size())
-            buf.copy_(src.view(torch.uint8).cpu())
-            host[name] = buf
-        outs = {"cand_event": pinned(wl.n_spans * f * 4), "cand_tier": pinned(wl.n_spans * f),
-                "attr": pinned(wl.n_spans * A.NSIG * 8), "conf": pinned(wl.n_spans * 8),
-                "inc_signals": pinned(wl.n_incidents * A.NSIG * 8), "posterior": pinned(wl.n_incidents * A.NDOM * 8),
-                "top1": pinned(wl.n_incidents), "counters": pinned(C.sizeof(A.Counters))}
-        hargs = A.PipelineArgs(host["spans"].data_ptr(), wl.n_spans, host["events"].data_ptr(), wl.n_events,
-                               host["idents"].data_ptr(), wl.n_idents, wl.n_incidents, host["inc_actual"].data_ptr(),
-                               host["inc_expected"].data_ptr(), host["inc_expected_n"].data_ptr(), 0, 0.0, f, 0.10,
-                               outs["cand_event"].data_ptr(), outs["cand_tier"].data_ptr(), outs["attr"].data_ptr(),
-                               outs["conf"].data_ptr(), outs["inc_signals"].data_ptr(), outs["posterior"].data_ptr(),
-                               outs["top1"].data_ptr(), outs["counters"].data_ptr())
-        h2d = sum(host[k].numel() for k in host)
-        d2h = sum(outs[k].numel() for k in outs)
-        hc = A.Counters()
-        for _ in range(2):
-            ctx.call_dev("lsg_pipeline", C.byref(hargs), C.byref(hc))
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        t_wall = time.perf_counter()
-        for _ in range(e2e_steps):
-            ctx.call_dev("lsg_pipeline", C.byref(hargs), C.byref(hc))
+            def pinned(nbytes):
+                return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, pin_memory=True)
+
+            for name in ("events", "spans", "idents", "inc_actual", "inc_expected", "inc_expected_n"):
+                src = getattr(wl, name)
+                buf = pinned(src.numel() * src.element_size())
+                buf.copy_(src.view(torch.uint8).cpu())
+                host[name] = buf
+            outs = {"cand_event": pinned(wl.n_spans * f * 4), "cand_tier": pinned(wl.n_spans * f),
+                    "attr": pinned(wl.n_spans * A.NSIG * 8), "conf": pinned(wl.n_spans * 8),
+                    "inc_signals": pinned(wl.n_incidents * A.NSIG * 8), "posterior": pinned(wl.n_incidents * A.NDOM * 8),
+                    "top1": pinned(wl.n_incidents), "counters": pinned(C.sizeof(A.Counters))}
+            hargs = A.PipelineArgs(host["spans"].data_ptr(), wl.n_spans, host["events"].data_ptr(), wl.n_events,
+                                   host["idents"].data_ptr(), wl.n_idents, wl.n_incidents, host["inc_actual"].data_ptr(),
+                                   host["inc_expected"].data_ptr(), host["inc_expected_n"].data_ptr(), 0, 0.0, f, 0.10,
+                                   outs["cand_event"].data_ptr(), outs["cand_tier"].data_ptr(), outs["attr"].data_ptr(),
+                                   outs["conf"].data_ptr(), outs["inc_signals"].data_ptr(), outs["posterior"].data_ptr(),
+                                   outs["top1"].data_ptr(), outs["counters"].data_ptr())
+            h2d = sum(host[k].numel() for k in host)
+            d2h = sum(outs[k].numel() for k in outs)
+            hc = A.Counters()
+            for _ in range(2):
+                ctx.call_dev("lsg_pipeline", C.byref(hargs), C.byref(hc))
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            t_wall = time.perf_counter()
+            for _ in range(e2e_steps):
+                ctx.call_dev("lsg_pipeline", C.byref(hargs), C.byref(hc))
+                if world > 1:
+                    dist.all_reduce(wl.counters, op=dist.ReduceOp.SUM)
+            e1.record(stream)
+            barrier()
+            t_wall = (time.perf_counter() - t_wall) * 1e3
+            e2e_ms = max(e0.elapsed_time(e1), 0.0)
+            t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
             if world > 1:
-                dist.all_reduce(wl.counters, op=dist.ReduceOp.SUM)
-        e1.record(stream)
-        barrier()
-        t_wall = (time.perf_counter() - t_wall) * 1e3
-        e2e_ms = max(e0.elapsed_time(e1), 0.0)
-        t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
-        e2e_ok = bytes(hc.confusion) == bytes(counters.confusion) if world == 1 else True
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+            e2e_ok = bytes(hc.confusion) == bytes(counters.confusion) if world == 1 else True
 
+        return {"value": wl.n_events * world * e2e_steps / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+                "wall_ms_per_step": t_wall / e2e_steps, "matches_device_run": bool(e2e_ok)}
+
+    e2e = None if args.no_e2e else measure_e2e()
+
+    f = 3
     n_events_total = wl.n_events * world
     value = n_events_total * args.steps / (ms_max / 1e3)
-    e2e_value = n_events_total * e2e_steps / (e2e_ms / 1e3)
 
     # ---- roofline of the dominant kernel -------------------------------------------------------------
     peak, peak_src = measured_peak_gbs()
@@ -312,8 +322,19 @@ def main():
     roofline = None
     if dom and dom in alg:
         achieved = per_kernel[dom]["GBps"]
+        # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this workload, if there is one
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic_%s.json" % args.workload)) as fh:
+                cap = json.load(fh)["kernels"]
+            sass = {"join": "k_join_tiles", "radix_scatter": "k_radix_scatter", "radix_hist": "k_radix_hist",
+                    "gather_events": "k_gather_events_soa"}.get(dom)
+            if sass in cap:
+                traffic = cap[sass]["dram_bytes_per_launch"]
+        except Exception:
+            traffic = None
         roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg[dom], "ms_per_launch": per_kernel[dom]["ms_per_launch"]}
     pipeline_alg = wl.algorithmic_bytes()
     end_to_end_frac = (pipeline_alg * args.steps / (ms_max / 1e3) / 1e9) / peak
@@ -348,9 +369,7 @@ def main():
                        "incidents_per_gpu": wl.n_incidents, "window_ms": 2000, "threshold": 0.7, "fanout": 3,
                        "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((wl.n_events + wl.n_spans) * 32 / 1e6),
                        "sort": sort_info, "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "wall_ms_per_step": t_wall / e2e_steps,
-                    "matches_device_run": bool(e2e_ok)},
+            "e2e": e2e,
             "gpu_launches": int(launches),
             "roofline": roofline,
             "pipeline_roofline": {"algorithmic_bytes_per_event": pipeline_alg / wl.n_events, "frac_of_peak": end_to_end_frac,

@@ -56,6 +56,7 @@ extern "C" int lsg_synth_dev(lsg_ctx *ctx, const lsg_synth_cfg *cfg, lsg_span *s
                              uint8_t *inc_actual, uint32_t *inc_expected, uint8_t *inc_expected_n) {
   if (!ctx) return LSG_ERR_INVALID;
   if (check_cfg(cfg)) return lsg_fail(ctx, LSG_ERR_INVALID, "invalid synthetic workload configuration");
+  LSG_CUDA(ctx, cudaSetDevice(ctx->device));
   const unsigned cap = (unsigned)ctx->sm_count * 8;
   auto grid = [&](size_t n) { size_t b = (n + 255) / 256; return (unsigned)(b > cap ? cap : (b ? b : 1)); };
   if (spans) { k_synth_spans<<<grid(cfg->n_spans), 256, 0, ctx->stream>>>(*cfg, spans); LSG_LAUNCH_CHECK(ctx); }
