@@ -114,9 +114,21 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
                        double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
                        unsigned long long *inc_keys = nullptr, size_t n_incidents = 0) {
-  LSG_TRY(lsg_sort_events(ctx, events, n_events, idents, n_idents, window_ns, false, nullptr, sorted));
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted));
+  // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
-  LSG_TRY(lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm));
+  {
+    LSG_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+    LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0));
+    cudaStream_t main_stream = ctx->stream;
+    ctx->stream = ctx->side;
+    const int rc = lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm);
+    ctx->stream = main_stream;
+    if (rc) return rc;
+    LSG_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->side));
+  }
+  LSG_TRY(lsg_sort_events_finish(ctx, events, n_events, idents, n_idents, nullptr, sorted));
+  LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
   void *small_v;
   LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
   JoinArgs ja;
@@ -201,6 +213,13 @@ int lsg_create(int device, void *stream, lsg_ctx **out) {
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return LSG_ERR_CUDA; }
     ctx->own_stream = true;
   }
+  if (cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return LSG_ERR_CUDA;
+  }
   ctx->pinned_cap = 8192;
   if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) {
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -224,6 +243,9 @@ void lsg_destroy(lsg_ctx *ctx) {
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (auto &sp : ctx->prof_open) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
   for (auto e : ctx->prof_pool) cudaEventDestroy(e);
+  if (ctx->side) { cudaStreamSynchronize(ctx->side); cudaStreamDestroy(ctx->side); }
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

@@ -40,6 +40,7 @@ enum {
   WS_IN4,
   WS_FEAT,           // incident feature accumulators
   WS_RANGES,         // per-span event ranges of the join
+  WS_SPAN_HIST,      // radix sort of the spans: per-tile digit histograms
   WS_COUNT
 };
 
@@ -96,6 +97,8 @@ struct lsg_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = false;
+  cudaStream_t side = nullptr;          // the span sort runs here, next to the event sort
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int sm_count = 148;
   std::string err;
   uint64_t launches = 0;
@@ -258,6 +261,10 @@ struct SortedEvents {
 // sorted_out != NULL: records (AoS) into sorted_out; NULL: columns (SoA) into the context workspace
 int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
                     bool exact, lsg_event *sorted_out, SortedEvents *out);
+int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                            int64_t window_ns, bool exact, SortedEvents *out);
+int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                           lsg_event *sorted_out, SortedEvents *out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,
                    const uint32_t **perm_out);
 struct JoinArgs {

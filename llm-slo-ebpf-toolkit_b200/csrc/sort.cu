@@ -58,6 +58,7 @@ k_event_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *_
   long long tmin = INT64_MAX, tmax = INT64_MIN;
   unsigned int live = 0, unsup = 0;
   bool bad = false;
+#pragma unroll 4
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     EventRec e = load_event(events + i);
     uint32_t g;
@@ -89,6 +90,7 @@ template <typename KeyT>
 __global__ void __launch_bounds__(256)
 k_event_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
              KeySpec ks, KeyT *__restrict__ keys) {
+#pragma unroll 4
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     EventRec e = load_event(events + i);
     uint32_t g;
@@ -417,6 +419,13 @@ int bits_of(uint64_t v) {
 // Sort events by (grp, quantised time).  Fills `out`; records land in `sorted_out` (or a workspace buffer if NULL).
 int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                     int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out));
+  return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out);
+}
+
+// phase 1: one pass over the events for the key layout (time range, group count) and the analytic counters
+int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                            int64_t window_ns, bool exact, SortedEvents *out) {
   memset(out, 0, sizeof *out);
   out->n = n;
   if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_events %zu does not fit 32-bit indices", n);
@@ -465,6 +474,13 @@ int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
                     (unsigned long long)range, st.max_grp);
   out->key = ks;
   ctx->last_key = ks;
+  return 0;
+}
+
+// phase 2: keys, radix passes, gather
+int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                           lsg_event *sorted_out, SortedEvents *out) {
+  const KeySpec ks = out->key;
   if (n == 0) return 0;
   const bool k32 = ks.bits <= 31;
   void *ka, *kb, *ia, *ib;
@@ -541,12 +557,12 @@ int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_iden
     k_span_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint32_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint32_t *ko;
-    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_SPAN_HIST, &ko, &perm));
   } else {
     k_span_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint64_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint64_t *ko;
-    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_SPAN_HIST, &ko, &perm));
   }
   *perm_out = perm;
   return 0;
