@@ -506,6 +506,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           }
         }
       }
+      __syncthreads();   // the hash pass (short, evenly spread) is complete: from here on a span only needs its own two lanes
       // ---- tiers 2-4: thread (2k + h) walks half h of span k's inner range
       const int k = i0 + (int)(tid >> 1);
       const unsigned h = tid & 1;
@@ -519,41 +520,47 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         if (rg.z < rg.w && rg.z != 0xffffffffu) {
           const lsg_ident sid = load_ident(p.idents, s.ident);
           const bool pod_ok = sid.pod != 0, svcnode_ok = sid.service != 0 && sid.node != 0;
+          const bool pid_ok = s.pid != 0, conn_ok = s.conn != 0;
           const uint32_t zo = rg.z - A, wo = rg.w - A;
           const uint32_t mid = zo + ((wo - zo) >> 1);
           const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
           const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
           const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);   // little endian: low words at even indices
+          const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;       // event trace ids are < 2^28
           for (uint32_t o = beg; o < end; ++o) {
-            uint64_t adt;
+            // every operand is loaded up front (five independent shared-memory loads), the decision is predicate arithmetic
+            const uint32_t e_trsig = sm.trsig[o], e_ident = sm.ident[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
+            bool in, in100, in250;
             if (T32) {   // |dt| < 2^31 ns for every event of an inner range: 32-bit arithmetic is exact
               const int32_t d = (int32_t)(ts_lo[2 * o] - s_lo);
-              adt = (uint32_t)(d < 0 ? -d : d);
+              const uint32_t ad = (uint32_t)(d < 0 ? -d : d);
+              in = ad <= (uint32_t)Wi; in100 = ad <= (uint32_t)(100 * kMs); in250 = ad <= (uint32_t)(250 * kMs);
             } else {
-              adt = lsg_absdiff(s.ts, sm.ts[o]);
+              const uint64_t ad = lsg_absdiff(s.ts, sm.ts[o]);
+              in = ad <= Wi; in100 = ad <= (uint64_t)(100 * kMs); in250 = ad <= (uint64_t)(250 * kMs);
             }
-            if (adt > Wi) continue;
-            if (s.trace != 0 && s.trace == (sm.trsig[o] >> 4)) continue;        // tier 1, taken by the hash pass
-            const uint32_t e_ident = sm.ident[o];
             bool same_pod = pod_ok, same_sn = svcnode_ok;
-            if (e_ident != s.ident) {
+            if (e_ident != s.ident) {   // another identity row: compare the interned strings
               const lsg_ident eid = load_ident(p.idents, e_ident);
               same_pod = pod_ok && sid.pod == eid.pod;
               same_sn = svcnode_ok && sid.service == eid.service && sid.node == eid.node;
             }
-            int tier = 0;
-            if (same_pod && s.pid != 0 && s.pid == sm.pid[o] && adt <= (uint64_t)(100 * kMs)) tier = LSG_TIER_POD_PID;          // dns.go:61-64
-            else if (same_pod && s.conn != 0 && s.conn == sm.conn[o] && adt <= (uint64_t)(250 * kMs)) tier = LSG_TIER_POD_CONN;  // dns.go:65-68
-            else if (same_sn) tier = LSG_TIER_SVC_NODE;                        // dns.go:69-73 (adt <= Wi <= 500 ms holds)
-            if (tier == 0) continue;                                           // Unmatched: counted analytically by the caller
-            n_match++;
-            if (tier > cut) { n_low++; continue; }                             // correlator.go:83-86
-            const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-            if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+            const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
+            const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
+            const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
+            // inside min(W, 500 ms), not a trace-id match (those belong to the hash pass), and some tier applies
+            const bool m = in & ((e_trsig >> 4) != no_trace) & (tier != 0);
+            n_match += m;
+            const bool low = m & (tier > cut);                                   // correlator.go:83-86
+            n_low += low;
+            if (m & !low) {
+              const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+              if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+            }
           }
         }
       }
-      __syncthreads();   // every note of the tile is in place
+      __syncwarp();      // the two lanes of a span sit in one warp: their notes are visible to each other now
       // ---- order: lane h takes the notes of parity h, then the odd lane hands its best F to the even lane
       TopF<F> top;
       top.init();
@@ -606,12 +613,17 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           }
           // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
           double v0 = nan, v3 = nan, v4 = nan;
+          unsigned present = 0;
+#pragma unroll
+          for (int r = 0; r < F; ++r) present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
 #pragma unroll
           for (int col = 0; col < LSG_NSIG; ++col) {
             double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
+            if ((present >> col) & 1u) {
 #pragma unroll
-            for (int r = 0; r < F; ++r)
-              if (sigs[r] == (unsigned)col && (isnan(v) || vals[r] > v)) v = vals[r];
+              for (int r = 0; r < F; ++r)
+                if (sigs[r] == (unsigned)col && (isnan(v) || vals[r] > v)) v = vals[r];
+            }
             p.attr_out[si * LSG_NSIG + col] = v;
             if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(v))
               atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
