@@ -296,6 +296,33 @@ int lsg_profile_enable(lsg_ctx *ctx, int on);
 const char *lsg_profile_name(int kind);
 int lsg_profile_read(lsg_ctx *ctx, double *ms, uint64_t *count, int cap, int reset);
 
+/* ---- rows either side of the path ---------------------------------------------------------
+ *
+ * F2  lsg_decode_ringbuf: the 40-byte packed little-endian struct llm_slo_event (ebpf/c/llm_slo_event.h:32-42,
+ *     bpfEvent in pkg/collector/ringbuf.go:42-52) -> lsg_event, doing what decodeBPFEvent + toProbeEvent +
+ *     signalFromType + convertValue do per record (ringbuf.go:152-238): kernel signal type 1..9 -> signal index,
+ *     ns -> ms except for counts and cpu_steal, ConnTuple present when a port is non-zero.  The metadata the agent
+ *     stamps on every event of one ring buffer (pod/node/service -> `ident`, trace id) are call arguments;
+ *     ts = timestamp_ns + ts_offset_ns (the reference stamps time.Now() at decode time, ringbuf.go:172, which a
+ *     replay cannot reproduce; pass the boot-time offset).  conn is a 32-bit mix of (src port, dst port, dst ip).
+ *     status_out (optional) is F4's code; errno_out (optional) the raw errno.
+ * F4  lsg_signal_status: signalStatus (pkg/signals/generator.go:203-242): 0 ok, 1 warning, 2 error.
+ * F1  lsg_retry_storm: RetryStormDetector.Record (pkg/correlation/retry_storm.go:46-62) replayed over a batch:
+ *     for every tcp_retransmits_total event, the number of retransmit events of the same pod with a time in
+ *     [ts - window, ts] that arrived no later, and whether that reaches `threshold`; 0 for other events.  Equals
+ *     the reference when each pod's events arrive in time order (its prefix-only pruning, retry_storm.go:98-110,
+ *     makes out-of-order arrivals order-dependent). */
+int lsg_decode_ringbuf(lsg_ctx *ctx, const void *raw /* n*40 bytes */, size_t n, uint32_t ident, uint32_t trace,
+                       int64_t ts_offset_ns, lsg_event *events_out, uint8_t *status_out, int32_t *errno_out);
+int lsg_decode_ringbuf_dev(lsg_ctx *ctx, const void *raw, size_t n, uint32_t ident, uint32_t trace, int64_t ts_offset_ns,
+                           lsg_event *events_out, uint8_t *status_out, int32_t *errno_out);
+int lsg_signal_status(lsg_ctx *ctx, const lsg_event *events, size_t n, uint8_t *status_out);
+int lsg_signal_status_dev(lsg_ctx *ctx, const lsg_event *events, size_t n, uint8_t *status_out);
+int lsg_retry_storm(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                    int64_t window_ns, int threshold, uint32_t *count_out, uint8_t *storm_out);
+int lsg_retry_storm_dev(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                        int64_t window_ns, int threshold, uint32_t *count_out, uint8_t *storm_out);
+
 /* ---- synthetic workload: record i is a pure function of (seed, i), generated on
  *      the device by lsg_synth_dev and on the host by lsg_synth_host with identical results. */
 typedef struct {

@@ -77,6 +77,12 @@ def load_library():
         lib.lsg_profile_name.argtypes = [cint]
         lib.lsg_profile_name.restype = C.c_char_p
         lib.lsg_profile_read.argtypes = [vp, P(C.c_double), P(C.c_uint64), cint, cint]
+        for name in ("lsg_decode_ringbuf", "lsg_decode_ringbuf_dev"):
+            getattr(lib, name).argtypes = [vp, vp, sz, C.c_uint32, C.c_uint32, i64, vp, vp, vp]
+        for name in ("lsg_signal_status", "lsg_signal_status_dev"):
+            getattr(lib, name).argtypes = [vp, vp, sz, vp]
+        for name in ("lsg_retry_storm", "lsg_retry_storm_dev"):
+            getattr(lib, name).argtypes = [vp, vp, sz, vp, sz, i64, cint, vp, vp]
         lib.lsg_incident_signals_static.argtypes = [vp, vp, vp, sz, sz, vp, C.c_char_p, sz]
         lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
         lib.lsg_abi_sizes.restype = cint
@@ -201,6 +207,33 @@ class Context:
                                             _ptr(posterior), float(coverage_thr), float(hyp_floor), len(actual),
                                             C.byref(out)))
         return out
+
+    def decode_ringbuf(self, raw, ident=0, trace=0, ts_offset_ns=0):
+        """raw: bytes / uint8 array of 40-byte llm_slo_event records -> (events, status, errno)"""
+        raw = np.frombuffer(raw, dtype=np.uint8) if isinstance(raw, (bytes, bytearray, memoryview)) else _as(raw, np.uint8)
+        if raw.size % 40:
+            raise ValueError("decode bpf event: %d bytes is not a multiple of the 40-byte record" % raw.size)
+        n = raw.size // 40
+        ev = np.zeros(n, A.EVENT_DTYPE)
+        st = np.zeros(n, np.uint8)
+        er = np.zeros(n, np.int32)
+        self._check(self._lib.lsg_decode_ringbuf(self._h, _ptr(np.ascontiguousarray(raw)), n, int(ident), int(trace),
+                                                 int(ts_offset_ns), _ptr(ev), _ptr(st), _ptr(er)))
+        return ev, st, er
+
+    def signal_status(self, events):
+        events = _as(events, A.EVENT_DTYPE)
+        st = np.zeros(len(events), np.uint8)
+        self._check(self._lib.lsg_signal_status(self._h, _ptr(events), len(events), _ptr(st)))
+        return st
+
+    def retry_storm(self, events, idents, window_ns, threshold):
+        events, idents = _as(events, A.EVENT_DTYPE), _as(idents, A.IDENT_DTYPE)
+        cnt = np.zeros(len(events), np.uint32)
+        storm = np.zeros(len(events), np.uint8)
+        self._check(self._lib.lsg_retry_storm(self._h, _ptr(events), len(events), _ptr(idents), len(idents), int(window_ns),
+                                              int(threshold), _ptr(cnt), _ptr(storm)))
+        return cnt, storm
 
     def last_sort_info(self):
         b, sh, ps = C.c_uint32(), C.c_uint32(), C.c_uint32()

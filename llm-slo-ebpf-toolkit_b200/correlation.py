@@ -229,3 +229,76 @@ def EvaluateGate(report: EvalReport, minPrecision: float, minRecall: float) -> G
     if report.Recall < minRecall:
         return GateResult(False, "recall gate failed: got %.4f required %.4f" % (report.Recall, minRecall))
     return GateResult(True, "correlation gate passed")
+
+
+# ---- pkg/correlation/retry_storm.go -------------------------------------------------------------------------
+DefaultStormWindow = 10 * SECOND      # retry_storm.go:9-10
+DefaultStormThreshold = 5             # retry_storm.go:12-14
+
+
+class RetryStormDetector:
+    """retry_storm.go:21-96.  RecordBatch is the GPU path: one sort by (pod, time) and one window count for the
+    whole batch (lsg_retry_storm).  Record / IsStorm / Count keep the reference's streaming interface on top of
+    it: the detector retains, per pod, the timestamps still inside the window (what the reference's bucket holds
+    after pruneOld) and prepends them to the next batch."""
+
+    def __init__(self, window: int, threshold: int, ctx=None):
+        self.window, self.threshold, self.ctx = window, threshold, ctx
+        self.buckets = {}
+
+    def RecordBatch(self, pods, timestamps):
+        """Record() for every (pod, ts) in arrival order; returns the list of Record's return values."""
+        if len(pods) == 0:
+            return []
+        ctx = self.ctx or default_context()
+        from .interner import to_ns
+        pod_ids = {}
+        hist_p, hist_t = [], []
+        for pod, ts_list in self.buckets.items():
+            for t in ts_list:
+                hist_p.append(pod)
+                hist_t.append(t)
+        all_p = hist_p + list(pods)
+        all_t = hist_t + [to_ns(t) for t in timestamps]
+        ev = np.zeros(len(all_p), A.EVENT_DTYPE)
+        for i, (pod, t) in enumerate(zip(all_p, all_t)):
+            ev[i] = (t, 1.0, pod_ids.setdefault(pod, len(pod_ids)), 0, 0, A.SIGNAL_INDEX["tcp_retransmits_total"])
+        idents = np.zeros(max(len(pod_ids), 1), A.IDENT_DTYPE)
+        for pod, row in pod_ids.items():
+            idents[row] = (row + 1, 0, 0, 1)
+        cnt, _storm = ctx.retry_storm(ev, idents, self.window, self.threshold)
+        out = [int(c) >= self.threshold for c in cnt[len(hist_p):]]
+        # what stays in each bucket: the events of the pod not older than its newest event minus the window
+        newest = {}
+        for pod, t in zip(all_p, all_t):
+            newest[pod] = t if pod not in newest else max(newest[pod], t)
+        self.buckets = {}
+        for pod, t in zip(all_p, all_t):
+            if t >= newest[pod] - self.window:
+                self.buckets.setdefault(pod, []).append(t)
+        return out
+
+    def Record(self, pod: str, ts) -> bool:
+        """retry_storm.go:46-62"""
+        return self.RecordBatch([pod], [ts])[0]
+
+    def Count(self, pod: str, now) -> int:
+        """retry_storm.go:80-90"""
+        from .interner import to_ns
+        if pod not in self.buckets:
+            return 0
+        now = to_ns(now)
+        self.buckets[pod] = [t for t in self.buckets[pod] if t >= now - self.window]
+        return len(self.buckets[pod])
+
+    def IsStorm(self, pod: str, now) -> bool:
+        """retry_storm.go:66-77"""
+        return pod in self.buckets and self.Count(pod, now) >= self.threshold
+
+    def Reset(self) -> None:
+        """retry_storm.go:93-96"""
+        self.buckets = {}
+
+
+def NewRetryStormDetector(window: int, threshold: int, ctx=None) -> RetryStormDetector:
+    return RetryStormDetector(window, threshold, ctx)

@@ -265,6 +265,8 @@ int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const 
                             int64_t window_ns, bool exact, SortedEvents *out);
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                            lsg_event *sorted_out, SortedEvents *out);
+int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, uint32_t sig,
+                           const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out, size_t *n_live_out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,
                    const uint32_t **perm_out);
 struct JoinArgs {

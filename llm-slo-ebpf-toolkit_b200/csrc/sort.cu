@@ -567,3 +567,108 @@ int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_iden
   *perm_out = perm;
   return 0;
 }
+
+// ---- F1 support: the events of one signal in stable (pod, exact time) order ---------------------------------
+namespace {
+struct PodStats { long long ts_min, ts_max; unsigned long long n_live; unsigned int max_pod, bad; unsigned int pad[2]; };
+
+__device__ __forceinline__ bool podtime_live(const EventRec &e, const lsg_ident *idents, uint32_t n_idents, uint32_t sig,
+                                             uint32_t *pod, bool *bad) {
+  *pod = 0;
+  if (e.ident >= n_idents) { *bad = true; return false; }
+  if ((e.trace_sig & 15u) != sig || e.ts == LSG_TS_ZERO) return false;
+  *pod = load_ident(idents, e.ident).pod;
+  return true;   // the reference keys its buckets by the pod string, empty or not (retry_storm.go:50-55)
+}
+
+__global__ void __launch_bounds__(256)
+k_podtime_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+                uint32_t sig, PodStats *st) {
+  long long tmin = INT64_MAX, tmax = INT64_MIN;
+  unsigned int live = 0, mp = 0;
+  bool bad = false;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const EventRec e = load_event(events + i);
+    uint32_t pod;
+    if (podtime_live(e, idents, n_idents, sig, &pod, &bad)) {
+      live++;
+      mp = max(mp, pod);
+      tmin = min(tmin, (long long)e.ts);
+      tmax = max(tmax, (long long)e.ts);
+    }
+  }
+  for (int o = 16; o; o >>= 1) {
+    tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+    tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+    live += __shfl_xor_sync(0xffffffffu, live, o);
+    mp = max(mp, __shfl_xor_sync(0xffffffffu, mp, o));
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&st->bad, 1u);
+  if ((threadIdx.x & 31) == 0 && live) {
+    atomicMin(&st->ts_min, tmin);
+    atomicMax(&st->ts_max, tmax);
+    atomicAdd(&st->n_live, (unsigned long long)live);
+    atomicMax(&st->max_pod, mp);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_podtime_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+               uint32_t sig, KeySpec ks, uint64_t *__restrict__ keys) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const EventRec e = load_event(events + i);
+    uint32_t pod;
+    bool bad = false;
+    uint64_t k = ks.dead;
+    if (podtime_live(e, idents, n_idents, sig, &pod, &bad)) k = lsg_make_key(ks, pod, e.ts);
+    keys[i] = k;
+  }
+}
+}  // namespace
+
+int lsg_sort_signal_by_pod(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                           uint32_t sig, const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out,
+                           size_t *n_live_out) {
+  *keys_out = nullptr; *perm_out = nullptr; *n_live_out = 0;
+  if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_events %zu does not fit 32-bit indices", n);
+  void *small_v = nullptr;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  PodStats *st_dev = (PodStats *)small_v;
+  PodStats *pin = (PodStats *)ctx->pinned;
+  memset(pin, 0, sizeof *pin);
+  pin->ts_min = INT64_MAX;
+  pin->ts_max = INT64_MIN;
+  LSG_CUDA(ctx, cudaMemcpyAsync(st_dev, pin, sizeof *pin, cudaMemcpyHostToDevice, ctx->stream));
+  if (n) {
+    k_podtime_stats<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, sig, st_dev);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  LSG_CUDA(ctx, cudaMemcpyAsync(pin, st_dev, sizeof *pin, cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const PodStats st = *pin;
+  if (st.bad) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
+  KeySpec ks;
+  ks.ts_min = st.n_live ? st.ts_min : 0;
+  ks.shift = 0;
+  ks.tbits = (uint32_t)bits_of(st.n_live ? (uint64_t)st.ts_max - (uint64_t)st.ts_min : 0);
+  if (ks.tbits == 0) ks.tbits = 1;
+  ks.bits = ks.tbits + bits_of((uint64_t)st.max_pod + 1);
+  ks.dead = ((uint64_t)st.max_pod + 1) << ks.tbits;
+  if (ks.bits > 62) return lsg_fail(ctx, LSG_ERR_RANGE, "(pod, time) key needs %u bits: more than 62", ks.bits);
+  *ks_out = ks;
+  *n_live_out = st.n_live;
+  if (n == 0) return 0;
+  void *ka, *kb, *ia, *ib;
+  LSG_TRY(lsg_ws(ctx, WS_KEYS_A, n * 8, &ka));
+  LSG_TRY(lsg_ws(ctx, WS_KEYS_B, n * 8, &kb));
+  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &ia));
+  LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4 + 64, &ib));
+  k_podtime_keys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, sig, ks, (uint64_t *)ka);
+  LSG_LAUNCH_CHECK(ctx);
+  uint64_t *ko;
+  uint32_t *perm;
+  LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_HIST, &ko, &perm));
+  *keys_out = ko;
+  *perm_out = perm;
+  return 0;
+}
