@@ -287,6 +287,13 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *args);
  * BuildConfusionMatrix cost a Go caller end to end (processor.go:29, pipeline.go:31,65). */
 int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *args, lsg_counters *counters_out);
 
+/* the same, double buffered: two slots (0, 1).  submit enqueues upload -> kernels -> download of one batch on three
+ * streams and returns; wait blocks until that batch's results are in the caller's buffers.  With two batches in
+ * flight the upload of one overlaps the kernels and the download of the other.  A slot's buffers must not be
+ * touched between submit and wait and should be pinned. */
+int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *args, int slot);
+int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out);
+
 /* ---- per-kernel timing with CUDA events on the context's stream (bench.py's roofline numbers) ---------
  *  lsg_profile_read synchronises the stream, adds the finished intervals to per-kernel totals and copies
  *  up to `cap` of them out (milliseconds, launches-groups counted); returns the number of kinds. */

@@ -73,6 +73,8 @@ def load_library():
         lib.lsg_synth_host.argtypes = [P(A.SynthCfg), vp, vp, vp, vp, vp, vp]
         lib.lsg_pipeline.argtypes = [vp, P(A.PipelineArgs), P(A.Counters)]
         lib.lsg_last_sort_info.argtypes = [vp, P(C.c_uint32), P(C.c_uint32), P(C.c_uint32)]
+        lib.lsg_pipeline_submit.argtypes = [vp, P(A.PipelineArgs), cint]
+        lib.lsg_pipeline_wait.argtypes = [vp, cint, P(A.Counters)]
         lib.lsg_profile_enable.argtypes = [vp, cint]
         lib.lsg_profile_name.argtypes = [cint]
         lib.lsg_profile_name.restype = C.c_char_p

@@ -244,6 +244,14 @@ void lsg_destroy(lsg_ctx *ctx) {
   for (auto &sp : ctx->prof_open) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
   for (auto e : ctx->prof_pool) cudaEventDestroy(e);
   if (ctx->side) { cudaStreamSynchronize(ctx->side); cudaStreamDestroy(ctx->side); }
+  if (ctx->up) { cudaStreamSynchronize(ctx->up); cudaStreamDestroy(ctx->up); }
+  if (ctx->down) { cudaStreamSynchronize(ctx->down); cudaStreamDestroy(ctx->down); }
+  for (int s = 0; s < 2; ++s) {
+    if (ctx->ev_up[s]) cudaEventDestroy(ctx->ev_up[s]);
+    if (ctx->ev_done[s]) cudaEventDestroy(ctx->ev_done[s]);
+    if (ctx->ev_down[s]) cudaEventDestroy(ctx->ev_down[s]);
+    if (ctx->slot_counters_host[s]) cudaFreeHost(ctx->slot_counters_host[s]);
+  }
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -616,6 +624,110 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   if (counters_out) memcpy(counters_out, ctx->pinned, sizeof(lsg_counters));
   if (a->counters_dev) memcpy(a->counters_dev, ctx->pinned, sizeof(lsg_counters));
+  return 0;
+}
+
+// ---- double-buffered form of lsg_pipeline -------------------------------------------------------------------
+// Two slots.  submit(slot) enqueues the upload of that batch on an upload stream, the kernels on the context's
+// stream (after the upload) and the download on a download stream (after the kernels), and returns; wait(slot)
+// blocks until the batch's results are in the caller's buffers.  With two batches in flight the upload of one,
+// the kernels of the other and the download of the previous one overlap (PCIe is full duplex), so the steady
+// state costs max(upload, kernels, download) per batch instead of their sum.  The caller's buffers of a slot
+// must stay untouched between submit and wait, and should be pinned (otherwise the copies serialise).
+}  // extern "C"
+namespace {
+enum { PB_EVENTS = 0, PB_SPANS, PB_IDENTS, PB_ACT, PB_EXP, PB_EXPN, PB_CE, PB_CT, PB_ATTR, PB_CONF, PB_SIG, PB_POST, PB_TOP1, PB_CNT, PB_BUFS };
+static_assert(PB_BUFS == 14, "WS_PIPE reserves 14 buffers per slot");
+
+int pipe_init(lsg_ctx *ctx) {
+  if (ctx->up) return 0;
+  LSG_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->up, cudaStreamNonBlocking));
+  LSG_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->down, cudaStreamNonBlocking));
+  for (int s = 0; s < 2; ++s) {
+    LSG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_up[s], cudaEventDisableTiming));
+    LSG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_done[s], cudaEventDisableTiming));
+    LSG_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_down[s], cudaEventDisableTiming));
+    LSG_CUDA(ctx, cudaMallocHost(&ctx->slot_counters_host[s], sizeof(lsg_counters)));
+  }
+  return 0;
+}
+template <typename T>
+int pipe_buf(lsg_ctx *ctx, int slot, int which, size_t n, T **out) {
+  void *p;
+  LSG_TRY(lsg_ws(ctx, WS_PIPE + slot * PB_BUFS + which, n * sizeof(T), &p));
+  *out = (T *)p;
+  return 0;
+}
+}  // namespace
+extern "C" {
+
+int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
+  if (!ctx || !a || slot < 0 || slot > 1) return LSG_ERR_INVALID;
+  if (!a->spans || !a->events || !a->idents || !a->inc_actual || !a->inc_expected || !a->inc_expected_n)
+    return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  if (ctx->slot_busy[slot]) return lsg_fail(ctx, LSG_ERR_INVALID, "slot %d is still in flight: call lsg_pipeline_wait first", slot);
+  LSG_TRY(set_device(ctx));
+  LSG_TRY(pipe_init(ctx));
+  const int f = a->fanout <= 0 ? 3 : a->fanout;
+  lsg_pipeline_args d = *a;
+  lsg_span *d_sp; lsg_event *d_ev; lsg_ident *d_id; uint8_t *d_act, *d_expn; uint32_t *d_exp;
+  LSG_TRY(pipe_buf(ctx, slot, PB_SPANS, a->n_spans, &d_sp));
+  LSG_TRY(pipe_buf(ctx, slot, PB_EVENTS, a->n_events, &d_ev));
+  LSG_TRY(pipe_buf(ctx, slot, PB_IDENTS, a->n_idents, &d_id));
+  LSG_TRY(pipe_buf(ctx, slot, PB_ACT, a->n_incidents, &d_act));
+  LSG_TRY(pipe_buf(ctx, slot, PB_EXP, a->n_incidents, &d_exp));
+  LSG_TRY(pipe_buf(ctx, slot, PB_EXPN, a->n_incidents, &d_expn));
+  LSG_TRY(pipe_buf(ctx, slot, PB_CE, a->n_spans * f, &d.cand_event));
+  LSG_TRY(pipe_buf(ctx, slot, PB_CT, a->n_spans * f, &d.cand_tier));
+  LSG_TRY(pipe_buf(ctx, slot, PB_ATTR, a->n_spans * LSG_NSIG, &d.attr_out));
+  LSG_TRY(pipe_buf(ctx, slot, PB_CONF, a->n_spans, &d.conf_out));
+  LSG_TRY(pipe_buf(ctx, slot, PB_SIG, a->n_incidents * LSG_NSIG, &d.inc_signals));
+  LSG_TRY(pipe_buf(ctx, slot, PB_POST, a->n_incidents * LSG_NDOM, &d.posterior));
+  LSG_TRY(pipe_buf(ctx, slot, PB_TOP1, a->n_incidents, &d.top1));
+  LSG_TRY(pipe_buf(ctx, slot, PB_CNT, (size_t)LSG_COUNTER_WORDS, &d.counters_dev));
+  // upload
+  auto up = [&](void *dst, const void *src, size_t bytes) -> int {
+    if (bytes) LSG_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->up));
+    return 0;
+  };
+  LSG_TRY(up(d_ev, a->events, a->n_events * sizeof(lsg_event)));
+  LSG_TRY(up(d_sp, a->spans, a->n_spans * sizeof(lsg_span)));
+  LSG_TRY(up(d_id, a->idents, a->n_idents * sizeof(lsg_ident)));
+  LSG_TRY(up(d_act, a->inc_actual, a->n_incidents));
+  LSG_TRY(up(d_exp, a->inc_expected, a->n_incidents * 4));
+  LSG_TRY(up(d_expn, a->inc_expected_n, a->n_incidents));
+  LSG_CUDA(ctx, cudaEventRecord(ctx->ev_up[slot], ctx->up));
+  // kernels
+  d.spans = d_sp; d.events = d_ev; d.idents = d_id; d.inc_actual = d_act; d.inc_expected = d_exp; d.inc_expected_n = d_expn;
+  LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_up[slot], 0));
+  LSG_TRY(lsg_pipeline_dev(ctx, &d));
+  LSG_CUDA(ctx, cudaEventRecord(ctx->ev_done[slot], ctx->stream));
+  // download
+  LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->down, ctx->ev_done[slot], 0));
+  auto down = [&](void *dst, const void *src, size_t bytes) -> int {
+    if (dst && bytes) LSG_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->down));
+    return 0;
+  };
+  LSG_TRY(down(a->cand_event, d.cand_event, a->n_spans * f * 4));
+  LSG_TRY(down(a->cand_tier, d.cand_tier, a->n_spans * f));
+  LSG_TRY(down(a->attr_out, d.attr_out, a->n_spans * LSG_NSIG * 8));
+  LSG_TRY(down(a->conf_out, d.conf_out, a->n_spans * 8));
+  LSG_TRY(down(a->inc_signals, d.inc_signals, a->n_incidents * LSG_NSIG * 8));
+  LSG_TRY(down(a->posterior, d.posterior, a->n_incidents * LSG_NDOM * 8));
+  LSG_TRY(down(a->top1, d.top1, a->n_incidents));
+  LSG_TRY(down(ctx->slot_counters_host[slot], d.counters_dev, sizeof(lsg_counters)));
+  LSG_CUDA(ctx, cudaEventRecord(ctx->ev_down[slot], ctx->down));
+  ctx->slot_busy[slot] = true;
+  return 0;
+}
+
+int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out) {
+  if (!ctx || slot < 0 || slot > 1) return LSG_ERR_INVALID;
+  if (!ctx->slot_busy[slot]) return lsg_fail(ctx, LSG_ERR_INVALID, "slot %d has nothing in flight", slot);
+  LSG_TRY(set_device(ctx));
+  LSG_CUDA(ctx, cudaEventSynchronize(ctx->ev_down[slot]));
+  ctx->slot_busy[slot] = false;
+  if (counters_out) memcpy(counters_out, ctx->slot_counters_host[slot], sizeof(lsg_counters));
   return 0;
 }
 

@@ -41,6 +41,8 @@ enum {
   WS_FEAT,           // incident feature accumulators
   WS_RANGES,         // per-span event ranges of the join
   WS_SPAN_HIST,      // radix sort of the spans: per-tile digit histograms
+  WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
+  WS_PIPE_END = WS_PIPE + 2 * 14 - 1,
   WS_COUNT
 };
 
@@ -98,6 +100,10 @@ struct lsg_ctx {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   cudaStream_t side = nullptr;          // the span sort runs here, next to the event sort
+  cudaStream_t up = nullptr, down = nullptr;                    // lsg_pipeline_submit: uploads / downloads next to the kernels
+  cudaEvent_t ev_up[2] = {}, ev_done[2] = {}, ev_down[2] = {};  // per slot: inputs on the device, kernels finished, results on the host
+  bool slot_busy[2] = {false, false};
+  void *slot_counters_host[2] = {};     // pinned, sizeof(lsg_counters) each
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   int sm_count = 148;
   std::string err;

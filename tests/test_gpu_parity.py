@@ -339,3 +339,61 @@ def test_full_c2_properties(ctx):
         assert np.array_equal(cand[sidx], wc)
         assert np.array_equal(tier[sidx], want["cand_tier"])
         assert np.array_equal(np.nan_to_num(attr[sidx], nan=-1e300), np.nan_to_num(want["attr"], nan=-1e300))
+
+
+def test_host_pipeline_blocking_and_double_buffered(ctx):
+    """lsg_pipeline (host buffers, blocking) and lsg_pipeline_submit / _wait (two batches in flight) give the device
+    pipeline's results, batch after batch."""
+    import torch
+    from llm_slo_ebpf_toolkit_b200.device import DeviceWorkload
+    batches = []
+    for seed in (1, 2, 3):
+        cfg = synth.config(300_000, 30_000, 32, 8, 2, seed=seed, horizon_ns=100_000_000_000, multi_fault=seed & 1)
+        w = synth.generate_host(cfg)
+        d = DeviceWorkload(ctx, cfg)
+        d.step()
+        torch.cuda.synchronize()
+        batches.append((cfg, w, d.read_counters(), d.host("cand_event", np.uint32).copy(), d.host("posterior", np.float64).copy()))
+    f = 3
+
+    def host_args(w):
+        ns, ni = len(w["spans"]), len(w["inc_actual"])
+        keep = {k: np.ascontiguousarray(w[k]) for k in ("spans", "events", "idents", "inc_actual", "inc_expected", "inc_expected_n")}
+        outs = {"ce": np.zeros(ns * f, np.uint32), "ct": np.zeros(ns * f, np.uint8), "attr": np.zeros(ns * A.NSIG), "conf": np.zeros(ns),
+                "sig": np.zeros(ni * A.NSIG), "post": np.zeros(ni * A.NDOM), "top1": np.zeros(ni, np.uint8)}
+        args = A.PipelineArgs(keep["spans"].ctypes.data, ns, keep["events"].ctypes.data, len(w["events"]), keep["idents"].ctypes.data,
+                              len(w["idents"]), ni, keep["inc_actual"].ctypes.data, keep["inc_expected"].ctypes.data,
+                              keep["inc_expected_n"].ctypes.data, 0, 0.0, f, 0.10, outs["ce"].ctypes.data, outs["ct"].ctypes.data,
+                              outs["attr"].ctypes.data, outs["conf"].ctypes.data, outs["sig"].ctypes.data, outs["post"].ctypes.data,
+                              outs["top1"].ctypes.data, None)
+        return args, keep, outs
+
+    def check(c, outs, ref):
+        _cfg, _w, rc, rce, rpost = ref
+        assert bytes(c) == bytes(rc)
+        assert np.array_equal(outs["ce"], rce[: len(outs["ce"])])
+        assert np.array_equal(np.nan_to_num(outs["post"], nan=-1.0), np.nan_to_num(rpost[: len(outs["post"])], nan=-1.0))
+
+    for ref in batches:                                   # blocking form
+        args, keep, outs = host_args(ref[1])
+        c = A.Counters()
+        ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(c))
+        check(c, outs, ref)
+    inflight = {}
+    order = [0, 1, 2, 1, 0, 2]                            # double-buffered form: six batches through two slots
+    for i, b in enumerate(order):
+        slot = i & 1
+        if slot in inflight:
+            c = A.Counters()
+            ctx.call_dev("lsg_pipeline_wait", slot, C.byref(c))
+            check(c, inflight[slot][2], batches[inflight[slot][0]])
+        args, keep, outs = host_args(batches[b][1])
+        ctx.call_dev("lsg_pipeline_submit", C.byref(args), slot)
+        inflight[slot] = (b, keep, outs, args)
+    for slot in (0, 1):
+        c = A.Counters()
+        ctx.call_dev("lsg_pipeline_wait", slot, C.byref(c))
+        check(c, inflight[slot][2], batches[inflight[slot][0]])
+    import llm_slo_ebpf_toolkit_b200 as pkg
+    with pytest.raises(pkg.LsgError):
+        ctx.call_dev("lsg_pipeline_wait", 0, None)        # nothing in flight
