@@ -328,11 +328,14 @@ def main():
     peak, peak_src = measured_peak_gbs()
     key_bytes = 4 if sort_info["key_bits"] <= 31 else 8
     n, s_, i_ = wl.n_events, wl.n_spans, wl.n_incidents
-    alg = {   # algorithmic bytes per launch (DESIGN.md §4): every operand read once, every result written once
-        "event_stats": 32 * n, "event_keys": (32 + key_bytes) * n, "radix_hist": key_bytes * n,
-        "radix_scatter": 2 * (key_bytes + 4) * n, "gather_events": (4 + 32 + 32) * n,
-        "join": 28 * n + 32 * s_ + 8 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # six columns once, span, range, outputs
-        "span_ranges": 32 * s_ + 8 * s_ + key_bytes * n,
+    counting = "event_keys" not in prof or prof["event_keys"][1] == 0   # counting sort (small key space) or radix passes
+    alg = {   # algorithmic bytes per launch (DESIGN.md §3): every operand read once, every result written once
+        "event_stats": 32 * n, "event_keys": (32 + key_bytes) * n,
+        "radix_hist": 32 * n if counting else key_bytes * n,                        # count keys: the records, once
+        "radix_scatter": (32 + 4) * n if counting else 2 * (key_bytes + 4) * n,     # place: record in, index out
+        "gather_events": (4 + 32 + 32) * n,
+        "join": 32 * n + 4 * n + 32 * s_ + 16 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # records + index once, span, ranges, outputs
+        "span_ranges": 32 * s_ + 16 * s_,
         "incident_features": A.NSIG * 8 * s_ + 4 * s_ + 2 * A.NSIG * 8 * i_, "attribute": (A.NSIG * 8 + A.NDOM * 8 + 1) * i_,
         "confusion": (A.NDOM * 8 + 7) * i_,
     }
@@ -393,7 +396,7 @@ def main():
             "config": {"workload": wl_name, "events_per_gpu": wl.n_events, "spans_per_gpu": wl.n_spans,
                        "incidents_per_gpu": wl.n_incidents, "window_ms": 2000, "threshold": 0.7, "fanout": 3,
                        "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((wl.n_events + wl.n_spans) * 32 / 1e6),
-                       "sort": sort_info, "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
+                       "sort": dict(sort_info, method="counting" if counting else "radix"), "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
             "e2e": e2e,
             "gpu_launches": int(launches),
             "roofline": roofline,

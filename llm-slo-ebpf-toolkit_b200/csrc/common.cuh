@@ -41,6 +41,8 @@ enum {
   WS_FEAT,           // incident feature accumulators
   WS_RANGES,         // per-span event ranges of the join
   WS_SPAN_HIST,      // radix sort of the spans: per-tile digit histograms
+  WS_BINS,           // counting sort: one counter per key
+  WS_SCAN,           // counting sort: block sums of the scan
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
   WS_PIPE_END = WS_PIPE + 2 * 14 - 1,
   WS_COUNT
@@ -249,28 +251,29 @@ LSG_HD uint64_t lsg_make_key(const KeySpec &k, uint32_t grp, int64_t ts) {
 // stage kernels (defined across the .cu files)
 int lsg_launch_match_pairs(lsg_ctx *, const lsg_span *, const lsg_event *, size_t, const lsg_ident *, size_t, int64_t, double,
                            const uint8_t *, const uint8_t *, uint8_t *, uint8_t *, uint64_t *eval_dev);
-struct EventColumns {     // events in key order as columns (what the join stages into shared memory)
+struct EventColumns {     // events grouped by key as columns (what the join stages into shared memory)
   const int64_t *ts;
   const double *val;
   const uint32_t *ident, *pid, *conn, *trsig;
 };
 struct SortedEvents {
-  EventColumns col;       // set when the sort was asked for columns
-  const lsg_event *rec;   // events in key order as records (set when the sort was asked for records)
-  const uint32_t *perm;   // sorted position -> input index
-  const void *keys;       // sorted keys (uint32_t if key.bits <= 32 else uint64_t)
+  EventColumns col;       // set when the records were not asked for (the join's input)
+  const lsg_event *rec;   // set when the caller asked for records (lsg_sort_events_dev)
+  const uint32_t *perm;   // position -> input index
+  const void *keys;       // radix path: the sorted keys (uint32_t if key.bits <= 31 else uint64_t); NULL on the counting path
+  const uint32_t *bins;   // counting path: bins[k] = end of key k's run (= start of key k + 1's); NULL on the radix path
   KeySpec key;
   size_t n;               // all events
-  size_t n_live;          // events that can match (sorted first)
+  size_t n_live;          // events that can match (they come first)
   uint64_t n_unsupported; // events with an unsupported signal type
 };
-// sorted_out != NULL: records (AoS) into sorted_out; NULL: columns (SoA) into the context workspace
+// sorted_out NULL: records into the context workspace.  `exact`: stable, nanosecond keys, always the radix path.
 int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
                     bool exact, lsg_event *sorted_out, SortedEvents *out);
 int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                             int64_t window_ns, bool exact, SortedEvents *out);
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                           lsg_event *sorted_out, SortedEvents *out);
+                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting);
 int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, uint32_t sig,
                            const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out, size_t *n_live_out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,

@@ -11,9 +11,10 @@
 // order nor the time quantisation can change the result.
 //
 // Two kernels:
-//   k_span_ranges  one thread per span (in key order): binary search of its outer range [a, b) (|dt| <= W, the
-//                  only place a trace-id match can be) and inner range [a2, b2) (|dt| <= min(W, 500 ms), the
-//                  only place tiers 2-4 can be) in the sorted keys.
+//   k_span_ranges  one thread per span (in key order): its outer range [a, b) (|dt| <= W, the only place a
+//                  trace-id match can be) and inner range [a2, b2) (|dt| <= min(W, 500 ms), the only place
+//                  tiers 2-4 can be): two reads of the counting sort's bin table, or binary searches in the
+//                  sorted keys on the radix path.
 //   k_join_tiles   a CTA takes 128 consecutive spans.  Their ranges overlap heavily (each event is inside
 //                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — six columns,
 //                  28 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier)
@@ -74,7 +75,8 @@ __device__ __forceinline__ uint32_t lower_bound_keys(const KeyT *__restrict__ ke
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ span_perm, size_t n_spans,
-              const KeyT *__restrict__ keys, uint32_t n_live, KeySpec ks, const lsg_ident *__restrict__ idents,
+              const KeyT *__restrict__ keys, const uint32_t *__restrict__ bins, uint32_t n_live, KeySpec ks,
+              const lsg_ident *__restrict__ idents,
               uint32_t n_idents, int64_t W, uint4 *__restrict__ ranges, unsigned long long *__restrict__ counters) {
   const uint64_t ts_max_q = ((uint64_t)1 << ks.tbits) - 1;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_spans; q += (size_t)gridDim.x * blockDim.x) {
@@ -104,8 +106,13 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
           if (qhi > ts_max_q) qhi = ts_max_q;
           const KeyT klo = (KeyT)(((uint64_t)grp << ks.tbits) | qlo);
           const KeyT khi = (KeyT)(((uint64_t)grp << ks.tbits) | qhi);
-          *pa = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, klo);
-          *pb = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, (KeyT)(khi + 1));
+          if (bins) {   // counting sort: bins[k] is the end of key k's run, i.e. the start of key k + 1's
+            *pa = klo ? bins[(uint32_t)klo - 1] : 0u;
+            *pb = bins[(uint32_t)khi];
+          } else {
+            *pa = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, klo);
+            *pb = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, (KeyT)(khi + 1));
+          }
         };
         search(W, 0, n_live, &r.x, &r.y);
         const int64_t Wi = W < 500 * kMs ? W : 500 * kMs;          // tiers 2-4: dns.go:62-73
@@ -714,11 +721,11 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
     if (blocks > cap) blocks = cap;
     if (a.ev.key.bits <= 31)
       k_span_ranges<uint32_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint32_t *)a.ev.keys,
-                                                                      n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
+                                                                      a.ev.bins, n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
                                                                       a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
     else
       k_span_ranges<uint64_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint64_t *)a.ev.keys,
-                                                                      n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
+                                                                      a.ev.bins, n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
                                                                       a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
     LSG_LAUNCH_CHECK(ctx);
   }

@@ -351,6 +351,146 @@ k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__rest
   for (; j < n; j += stride) put(j, ld_nc_v8(events + perm[j]));
 }
 
+// ---- counting sort (small key spaces) --------------------------------------------------------------------------
+// With the coarse time quantum the whole key space of a batch is a few million values: one counter per key fits
+// in L2, so "sort" is: count the keys (L2 atomics), exclusive scan, place every record at a cursor fetch-add.
+// Three light passes instead of keys + 3 x (histogram, scan, scatter) + gather, and a span's event range becomes
+// two table reads.  The order of the events inside one key is whatever the atomics give: the join does not care
+// (it selects by an explicit total order), and lsg_sort_events_dev never takes this path.
+constexpr uint32_t COUNTING_MAX_KEYS = 1u << 25;   // 128 MB of counters at most
+
+__global__ void __launch_bounds__(256)
+k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+             KeySpec ks, uint32_t *__restrict__ bins) {
+#pragma unroll 2
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const EventRec e = load_event(events + i);
+    uint32_t g;
+    bool bad = false;
+    if (event_live(e, idents, n_idents, &g, &bad)) atomicAdd(&bins[(uint32_t)lsg_make_key(ks, g, e.ts)], 1u);
+  }
+}
+
+// Only the permutation is scattered (4-byte writes into an array that stays in L2); the 32-byte records are moved
+// afterwards by the gather: random READS of records are cheap, random 32-byte WRITES into a 320 MB output are not
+// (measured: 0.74 ms for 10 M records against 0.28 ms for the gather).
+__global__ void __launch_bounds__(256)
+k_place_events(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+               KeySpec ks, uint32_t *__restrict__ bins, uint32_t *__restrict__ perm) {
+#pragma unroll 2
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const EventRec e = load_event(events + i);
+    uint32_t g;
+    bool bad = false;
+    if (event_live(e, idents, n_idents, &g, &bad)) {
+      const uint32_t pos = atomicAdd(&bins[(uint32_t)lsg_make_key(ks, g, e.ts)], 1u);   // cursor: ends as the run's end
+      perm[pos] = (uint32_t)i;
+    }
+  }
+}
+
+// exclusive scan of n 32-bit counters in place: block sums, scan of the sums, local scan + offset
+constexpr int SCAN_BLOCK = 256, SCAN_IPT = 16, SCAN_TILE = SCAN_BLOCK * SCAN_IPT;
+
+__global__ void __launch_bounds__(SCAN_BLOCK)
+k_scan_reduce(const uint32_t *__restrict__ data, size_t n, uint32_t *__restrict__ block_sums) {
+  __shared__ uint32_t s_w[SCAN_BLOCK / 32];
+  const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_IPT;
+  uint32_t t = 0;
+  if (base + SCAN_IPT <= n) {
+#pragma unroll
+    for (int q = 0; q < SCAN_IPT / 4; ++q) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(data + base + 4 * q);
+      t += v.x + v.y + v.z + v.w;
+    }
+  } else {
+    for (int q = 0; q < SCAN_IPT; ++q)
+      if (base + q < n) t += data[base + q];
+  }
+  t = __reduce_add_sync(0xffffffffu, t);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t b = 0;
+    for (int w = 0; w < SCAN_BLOCK / 32; ++w) b += s_w[w];
+    block_sums[blockIdx.x] = b;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_scan_sums(uint32_t *__restrict__ sums, uint32_t n) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_carry;
+  if (threadIdx.x == 0) s_carry = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t base = 0; base < n; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < n ? sums[i] : 0;
+    uint32_t x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= (unsigned)o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      const uint32_t w = s_warp[lane];
+      uint32_t z = w;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, z, o);
+        if (lane >= (unsigned)o) z += y;
+      }
+      s_warp[lane] = z - w;
+    }
+    __syncthreads();
+    const uint32_t carry = s_carry;
+    if (i < n) sums[i] = carry + s_warp[warp] + x - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) s_carry = carry + s_warp[warp] + x;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_BLOCK)
+k_scan_apply(uint32_t *__restrict__ data, size_t n, const uint32_t *__restrict__ block_sums) {
+  __shared__ uint32_t s_w[SCAN_BLOCK / 32];
+  const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_IPT;
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t v[SCAN_IPT];
+  const bool full = base + SCAN_IPT <= n;
+  if (full) {
+#pragma unroll
+    for (int q = 0; q < SCAN_IPT / 4; ++q) {
+      const uint4 u = *reinterpret_cast<const uint4 *>(data + base + 4 * q);
+      v[4 * q] = u.x; v[4 * q + 1] = u.y; v[4 * q + 2] = u.z; v[4 * q + 3] = u.w;
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < SCAN_IPT; ++q) v[q] = base + q < n ? data[base + q] : 0;
+  }
+  uint32_t t = 0;
+#pragma unroll
+  for (int q = 0; q < SCAN_IPT; ++q) { const uint32_t c = v[q]; v[q] = t; t += c; }   // exclusive within the thread
+  uint32_t x = t;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= (unsigned)o) x += y;
+  }
+  if (lane == 31) s_w[warp] = x;
+  __syncthreads();
+  uint32_t pre = block_sums[blockIdx.x] + x - t;
+  for (unsigned w = 0; w < warp; ++w) pre += s_w[w];
+  if (full) {
+#pragma unroll
+    for (int q = 0; q < SCAN_IPT / 4; ++q)
+      *reinterpret_cast<uint4 *>(data + base + 4 * q) = make_uint4(pre + v[4 * q], pre + v[4 * q + 1], pre + v[4 * q + 2], pre + v[4 * q + 3]);
+  } else {
+#pragma unroll
+    for (int q = 0; q < SCAN_IPT; ++q)
+      if (base + q < n) data[base + q] = pre + v[q];
+  }
+}
+
 size_t scatter_smem(size_t key_bytes) {
   return (size_t)(SORT_NW * RADIX + RADIX + RADIX + 8 + SORT_TILE) * 4 + (size_t)SORT_TILE * key_bytes;
 }
@@ -420,7 +560,7 @@ int bits_of(uint64_t v) {
 int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                     int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out));
-  return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out);
+  return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out, !exact);
 }
 
 // phase 1: one pass over the events for the key layout (time range, group count) and the analytic counters
@@ -477,16 +617,73 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
   return 0;
 }
 
-// phase 2: keys, radix passes, gather
+// phase 2: place the events.  Counting sort when the key space is small (and the caller does not need a stable,
+// exact order), else keys + radix passes + gather.
 int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                           lsg_event *sorted_out, SortedEvents *out) {
+                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting) {
   const KeySpec ks = out->key;
   if (n == 0) return 0;
+  // where the events go: the caller's record array, or columns in the workspace (padded so that a 16-byte aligned
+  // bulk copy may run a little past the last event)
+  int64_t *c_ts = nullptr; double *c_val = nullptr; uint32_t *c_ident = nullptr, *c_pid = nullptr, *c_conn = nullptr, *c_trsig = nullptr;
+  if (!sorted_out) {
+    const size_t n_pad = ((n + 3) & ~(size_t)3) + 4;
+    void *sv;
+    LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n_pad * 32, &sv));
+    char *base = (char *)sv;
+    c_ts = (int64_t *)base;
+    c_val = (double *)(base + 8 * n_pad);
+    c_ident = (uint32_t *)(base + 16 * n_pad); c_pid = (uint32_t *)(base + 20 * n_pad);
+    c_conn = (uint32_t *)(base + 24 * n_pad); c_trsig = (uint32_t *)(base + 28 * n_pad);
+    out->col = EventColumns{c_ts, c_val, c_ident, c_pid, c_conn, c_trsig};
+  } else {
+    out->rec = sorted_out;
+  }
+  auto gather = [&](const uint32_t *perm, size_t count) -> int {
+    ProfScope ps(ctx, PK_GATHER);
+    if (sorted_out) k_gather_events<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, sorted_out);
+    else k_gather_events_soa<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
+    LSG_LAUNCH_CHECK(ctx);
+    return 0;
+  };
+  if (allow_counting && ks.shift != 0 && ks.dead <= COUNTING_MAX_KEYS) {
+    const size_t n_keys = (size_t)ks.dead;   // live keys are < dead
+    void *bv, *sv, *pv;
+    LSG_TRY(lsg_ws(ctx, WS_BINS, (n_keys + SCAN_TILE) * 4, &bv));
+    const uint32_t n_blocks = (uint32_t)((n_keys + SCAN_TILE - 1) / SCAN_TILE);
+    LSG_TRY(lsg_ws(ctx, WS_SCAN, (size_t)n_blocks * 4 + 64, &sv));
+    LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &pv));
+    uint32_t *bins = (uint32_t *)bv, *sums = (uint32_t *)sv, *perm = (uint32_t *)pv;
+    {
+      ProfScope ps(ctx, PK_HIST);
+      LSG_CUDA(ctx, cudaMemsetAsync(bins, 0, n_keys * 4, ctx->stream));
+      k_count_keys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, bins);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    {
+      ProfScope ps(ctx, PK_SCAN);
+      k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(bins, n_keys, sums);
+      LSG_LAUNCH_CHECK(ctx);
+      k_scan_sums<<<1, 1024, 0, ctx->stream>>>(sums, n_blocks);
+      LSG_LAUNCH_CHECK(ctx);
+      k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(bins, n_keys, sums);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    {
+      ProfScope ps(ctx, PK_SCATTER);
+      k_place_events<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, bins, perm);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    if (out->n_live) LSG_TRY(gather(perm, out->n_live));
+    out->bins = bins;
+    out->perm = perm;
+    return 0;
+  }
   const bool k32 = ks.bits <= 31;
   void *ka, *kb, *ia, *ib;
   LSG_TRY(lsg_ws(ctx, WS_KEYS_A, n * (k32 ? 4 : 8), &ka));
   LSG_TRY(lsg_ws(ctx, WS_KEYS_B, n * (k32 ? 4 : 8), &kb));
-  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &ia));   // + padding: the join's bulk copies run up to 3 entries past n
+  LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &ia));
   LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4 + 64, &ib));
   uint32_t *perm = nullptr;
   if (k32) {
@@ -509,29 +706,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
     out->keys = ko;
   }
   out->perm = perm;
-  if (!sorted_out) {
-    // columns, padded so that a 16-byte aligned bulk copy may run a little past the last event
-    const size_t n_pad = ((n + 3) & ~(size_t)3) + 4;
-    void *sv;
-    LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n_pad * 32, &sv));
-    char *base = (char *)sv;
-    int64_t *c_ts = (int64_t *)base;
-    double *c_val = (double *)(base + 8 * n_pad);
-    uint32_t *c_ident = (uint32_t *)(base + 16 * n_pad), *c_pid = (uint32_t *)(base + 20 * n_pad);
-    uint32_t *c_conn = (uint32_t *)(base + 24 * n_pad), *c_trsig = (uint32_t *)(base + 28 * n_pad);
-    ProfScope ps(ctx, PK_GATHER);
-    k_gather_events_soa<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
-    LSG_LAUNCH_CHECK(ctx);
-    out->col = EventColumns{c_ts, c_val, c_ident, c_pid, c_conn, c_trsig};
-    return 0;
-  }
-  {
-    ProfScope ps(ctx, PK_GATHER);
-    k_gather_events<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, perm, n, sorted_out);
-    LSG_LAUNCH_CHECK(ctx);
-  }
-  out->rec = sorted_out;
-  return 0;
+  return gather(perm, n);
 }
 
 // Processing order of the spans: same key as the events, so consecutive spans read overlapping event ranges.
