@@ -331,8 +331,8 @@ def main():
     counting = "event_keys" not in prof or prof["event_keys"][1] == 0   # counting sort (small key space) or radix passes
     alg = {   # algorithmic bytes per launch: every operand read once, every result written once
         "event_stats": 32 * n, "event_keys": (32 + key_bytes) * n,
-        "radix_hist": 32 * n if counting else key_bytes * n,                        # count keys: the records, once
-        "radix_scatter": (32 + 4) * n if counting else 2 * (key_bytes + 4) * n,     # place: record in, index out
+        "radix_hist": (32 + 8) * n if counting else key_bytes * n,                  # count keys: the records once, (key, rank) out
+        "radix_scatter": (8 + 4) * n if counting else 2 * (key_bytes + 4) * n,      # place: (key, rank) in, index out
         "gather_events": (4 + 32 + 32) * n,
         "join": 32 * n + 4 * n + 32 * s_ + 16 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # records + index once, span, ranges, outputs
         "span_ranges": 32 * s_ + 16 * s_,

@@ -261,7 +261,7 @@ struct SortedEvents {
   const lsg_event *rec;   // set when the caller asked for records (lsg_sort_events_dev)
   const uint32_t *perm;   // position -> input index
   const void *keys;       // radix path: the sorted keys (uint32_t if key.bits <= 31 else uint64_t); NULL on the counting path
-  const uint32_t *bins;   // counting path: bins[k] = end of key k's run (= start of key k + 1's); NULL on the radix path
+  const uint32_t *bins;   // counting path: bins[k] = start of key k's run, bins[k + 1] its end; NULL on the radix path
   KeySpec key;
   size_t n;               // all events
   size_t n_live;          // events that can match (they come first)

@@ -106,9 +106,9 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
           if (qhi > ts_max_q) qhi = ts_max_q;
           const KeyT klo = (KeyT)(((uint64_t)grp << ks.tbits) | qlo);
           const KeyT khi = (KeyT)(((uint64_t)grp << ks.tbits) | qhi);
-          if (bins) {   // counting sort: bins[k] is the end of key k's run, i.e. the start of key k + 1's
-            *pa = klo ? bins[(uint32_t)klo - 1] : 0u;
-            *pb = bins[(uint32_t)khi];
+          if (bins) {   // counting sort: bins[k] is the start of key k's run
+            *pa = bins[(uint32_t)klo];
+            *pb = bins[(uint32_t)khi + 1];
           } else {
             *pa = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, klo);
             *pb = lo_pos + lower_bound_keys<KeyT>(keys + lo_pos, hi_pos - lo_pos, (KeyT)(khi + 1));
