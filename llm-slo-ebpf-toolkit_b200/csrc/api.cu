@@ -3,6 +3,7 @@
 // file only moves buffers, validates arguments and launches.  No CPU fallback.
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <new>
 
 #include "common.cuh"

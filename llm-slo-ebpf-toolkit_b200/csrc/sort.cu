@@ -364,12 +364,32 @@ constexpr uint32_t COUNTING_MAX_KEYS = 1u << 25;   // 128 MB of counters at most
 __global__ void __launch_bounds__(256)
 k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
              KeySpec ks, uint32_t *__restrict__ bins, uint2 *__restrict__ key_rank) {
-#pragma unroll 2
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  // the returning atomic has L2 round-trip latency: four events per thread in flight
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    EventRec e[4];
+    uint2 kr[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) e[u] = load_event(events + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint32_t g;
+      bool bad = false;
+      kr[u] = make_uint2(0xffffffffu, 0u);   // not placed: matches nothing
+      if (event_live(e[u], idents, n_idents, &g, &bad)) kr[u].x = (uint32_t)lsg_make_key(ks, g, e[u].ts);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (kr[u].x != 0xffffffffu) kr[u].y = atomicAdd(&bins[kr[u].x], 1u);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) key_rank[i + u * stride] = kr[u];
+  }
+  for (; i < n; i += stride) {
     const EventRec e = load_event(events + i);
     uint32_t g;
     bool bad = false;
-    uint2 kr = make_uint2(0xffffffffu, 0u);   // not placed: matches nothing
+    uint2 kr = make_uint2(0xffffffffu, 0u);
     if (event_live(e, idents, n_idents, &g, &bad)) {
       kr.x = (uint32_t)lsg_make_key(ks, g, e.ts);
       kr.y = atomicAdd(&bins[kr.x], 1u);
@@ -384,7 +404,21 @@ k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
 // (measured: 0.74 ms for 10 M records against 0.28 ms for the gather).
 __global__ void __launch_bounds__(256)
 k_place_events(const uint2 *__restrict__ key_rank, size_t n, const uint32_t *__restrict__ bins, uint32_t *__restrict__ perm) {
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+  // two dependent random accesses per event (run start, then the permutation slot): four events per thread in flight
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    uint2 kr[4];
+    uint32_t start[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) kr[u] = key_rank[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) start[u] = kr[u].x != 0xffffffffu ? __ldg(bins + kr[u].x) : 0u;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (kr[u].x != 0xffffffffu) perm[start[u] + kr[u].y] = (uint32_t)(i + u * stride);
+  }
+  for (; i < n; i += stride) {
     const uint2 kr = key_rank[i];
     if (kr.x != 0xffffffffu) perm[__ldg(bins + kr.x) + kr.y] = (uint32_t)i;
   }
