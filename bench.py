@@ -126,7 +126,7 @@ def cpu_pass(w, brute, nthreads):
     return O.confusion(w["inc_actual"], top1, w["inc_expected"], w["inc_expected_n"], post, 0.10, 0.01)
 
 
-def run_reference(args):
+def run_reference(args, out):
     """--impl reference: the reference's own algorithm for the path — every span against every signal
     (ebpfcorrelator/processor.go:29-49, correlator.go:72-90), then AttributeSample and BuildConfusionMatrix —
     as restated in oracle/oracle.cpp (Go is not installed, so the reference itself cannot run), on all host
@@ -160,11 +160,22 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "checks": {"incidents": int(conf.n), "correct": int(conf.correct)},
     }
-    print(json.dumps(line))
+    out.write(json.dumps(line) + "\n")
+    out.flush()
     return 0
 
 
+def _claim_stdout():
+    """Libraries (NCCL prints its version) write to fd 1; the contract is ONE JSON line there.  Keep a private handle
+    on the real stdout for that line and point fd 1 at stderr for everything else."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 def main():
+    out = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -176,7 +187,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer measurement (C3 needs 37 GB of pinned memory)")
     args = ap.parse_args()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, out)
     args.warmup = max(args.warmup, 3)
 
     import numpy as np
@@ -210,12 +221,34 @@ def main():
     with torch.cuda.stream(stream):
         wl = DeviceWorkload(ctx, cfg)
 
+        # The only exchange of the path is the sum of the counter block (N > 1).  Two blocks alternate, so the allreduce of
+        # batch k (asynchronous, on NCCL's stream) overlaps the kernels of batch k + 1; it is waited for before its
+        # block is reused, and every batch's reduction completes inside the timed region.
+        blocks = [wl.counters, torch.zeros_like(wl.counters)]
+        pending = [None, None]
+        state = {"i": 0}
+
         def step():
+            b = state["i"] & 1
+            state["i"] += 1
+            if pending[b] is not None:
+                pending[b].wait()
+                pending[b] = None
+            wl.args.counters_dev = blocks[b].data_ptr()
             wl.step()
-            sharding.allreduce_counters(wl.counters)   # the only exchange of the path: sum of the counter block (N > 1)
+            if world > 1:
+                pending[b] = dist.all_reduce(blocks[b], op=dist.ReduceOp.SUM, async_op=True)
+
+        def drain():
+            for b in (0, 1):
+                if pending[b] is not None:
+                    pending[b].wait()
+                    pending[b] = None
+            wl.counters = blocks[(state["i"] - 1) & 1]   # the most recent batch's (reduced) block
 
         for _ in range(args.warmup):
             step()
+        drain()
         barrier()
         sort_info = ctx.last_sort_info()
         ctx.profile_read(reset=True)
@@ -227,6 +260,7 @@ def main():
         ev0.record(stream)
         for _ in range(args.steps):
             step()
+        drain()
         ev1.record(stream)
         barrier()
         clocks = sampler.stop()
@@ -409,7 +443,8 @@ def main():
                        "candidates": int(counters.candidates), "kept": int(counters.kept),
                        "low_confidence": int(counters.debug.low_confidence)},
         }
-        print(json.dumps(line))
+        out.write(json.dumps(line) + "\n")
+        out.flush()
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
