@@ -48,7 +48,7 @@ extern "C" {
 #define LSG_TRACE_BITS 28      /* events pack trace id and signal into one word                            */
 #define LSG_TS_ZERO INT64_MIN  /* time.Time{}.IsZero() (dns.go:108); Unix 0 is a valid time                */
 #define LSG_NONE 0xFFFFFFFFu   /* "no event" / "no incident"                                               */
-#define LSG_MAX_FANOUT 8
+#define LSG_MAX_FANOUT 32     /* MaxJoinFanout accepted; up to 8 runs on the tile kernel, 9..32 on the warp-per-span kernel */
 #define LSG_MAX_ACTUAL 16      /* rows of the confusion matrix: 8 domains + up to 8 other actual strings   */
 #define LSG_MAX_WINDOW_NS (((int64_t)1 << 53) - 1) /* float64(Duration) compare in dns.go:111-112 is exact below this */
 

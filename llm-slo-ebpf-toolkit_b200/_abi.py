@@ -10,7 +10,7 @@ SIG_UNSUPPORTED = 15
 TRACE_BITS = 28
 TS_ZERO = -(1 << 63)
 NONE = 0xFFFFFFFF
-MAX_FANOUT = 8
+MAX_FANOUT = 32
 MAX_ACTUAL = 16
 MAX_WINDOW_NS = (1 << 53) - 1
 SKETCH_BINS = 16

@@ -26,6 +26,7 @@
 //                  not fit a tile is scanned straight from global memory by the same code.
 // Outputs are written at the span's input position; optionally the per-incident maxima (A7 glue) are
 // accumulated from the epilogue with one atomicMax per present attribute.
+#include <algorithm>
 #include <cmath>
 
 #include "common.cuh"
@@ -359,6 +360,7 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
 // does not fit a tile) is left to k_join_big.
 constexpr int TM_CAP = 1920;    // events per tile
 constexpr int TM_LIST = 48;     // noted candidates per span
+constexpr int TM_MAX_F = 8;      // largest fanout the tile kernel keeps in registers
 constexpr int TM_HASH = 256;    // hash slots for the chunk's span trace ids (<= 128 keys)
 constexpr uint16_t TM_END = 0xffffu;
 
@@ -679,6 +681,11 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
   if (tid < 5 && sm.cnt[tid]) atomicAdd(&p.counters[tid], sm.cnt[tid]);
 }
 
+__global__ void k_list_all_spans(uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count, uint32_t n) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) big_list[i] = i;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *big_count = n;
+}
+
 // ---- spans whose own range exceeds a tile: one warp per span, straight from global memory ---------------
 __global__ void __launch_bounds__(JT_THREADS)
 k_join_big(const __grid_constant__ JoinParams p, const uint32_t *__restrict__ big_list, const unsigned int *__restrict__ big_count) {
@@ -760,8 +767,12 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   const bool t32 = a.ev.key.shift < 29 && wi + ((int64_t)2 << a.ev.key.shift) < ((int64_t)1 << 31);
   if (a.fanout <= 3) {
     if (t32) LSG_TRY(launch(k_join_tiles<3, true>)); else LSG_TRY(launch(k_join_tiles<3, false>));
+  } else if (a.fanout <= TM_MAX_F) {
+    if (t32) LSG_TRY(launch(k_join_tiles<TM_MAX_F, true>)); else LSG_TRY(launch(k_join_tiles<TM_MAX_F, false>));
   } else {
-    if (t32) LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT, true>)); else LSG_TRY(launch(k_join_tiles<LSG_MAX_FANOUT, false>));
+    // more kept candidates than the tile kernel holds in registers: every span goes to the warp-per-span kernel
+    k_list_all_spans<<<(unsigned)std::min<size_t>((a.n_spans + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+        big_list, big_count, (uint32_t)a.n_spans);
   }
   LSG_LAUNCH_CHECK(ctx);
   {
