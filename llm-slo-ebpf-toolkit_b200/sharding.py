@@ -64,3 +64,29 @@ def ratios(c):
         for ln in range(1, A.NDOM + 1):
             cov += int(c.confusion.coverage[f][ln]) * (float(f) / float(ln))
     return {"accuracy": c.confusion.correct / n, "partial": c.confusion.partial / n, "coverage": cov / n}
+
+
+def exchange(records, owner, group=None):
+    """All-to-all of packed records for input that arrives unsharded (the optional pre-step): every
+    rank holds an arbitrary slice of the batch; `owner[i]` is the rank that must process records[i] (shard_of_group of
+    its join group).  Returns (received records, source rank of each, index of each in its source slice).
+    `records` is a torch tensor [n, k] of any dtype (32-byte records as 4 x int64 or 32 x uint8) on the device the
+    process group works on (CUDA for NCCL, CPU for gloo)."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    owner = owner.to(torch.int64)
+    order = torch.argsort(owner, stable=True)
+    send = records[order].contiguous()
+    send_idx = order.to(torch.int64)
+    counts = torch.bincount(owner, minlength=world).to(torch.int64)
+    recv_counts = torch.empty_like(counts)
+    dist.all_to_all_single(recv_counts, counts, group=group)
+    sc, rc = counts.tolist(), recv_counts.tolist()
+    out = records.new_empty((int(sum(rc)),) + tuple(records.shape[1:]))
+    dist.all_to_all_single(out, send, output_split_sizes=rc, input_split_sizes=sc, group=group)
+    idx = send_idx.new_empty(int(sum(rc)))
+    dist.all_to_all_single(idx, send_idx, output_split_sizes=rc, input_split_sizes=sc, group=group)
+    src = torch.repeat_interleave(torch.arange(world, device=idx.device), torch.tensor(rc, device=idx.device))
+    return out, src, idx

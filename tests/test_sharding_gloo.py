@@ -78,3 +78,42 @@ def test_partition_by_group_is_exact():
     assert low == whole.debug.low_confidence and kept == whole.kept
     own = sharding.shard_of_group(np.arange(1, 4097), 8)
     assert np.bincount(own, minlength=8).min() > 400           # even spread of consecutive group ids
+
+
+def _exchange_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # one batch, arriving unsharded: rank r holds every world-th record
+    w = synth.generate_host(synth.config(40_000, 4_000, 32, 8, 2, seed=9, horizon_ns=5_000_000_000))
+    owner = sharding.shard_of_group(w["idents"]["grp"], world)
+    parts = {}
+    for name, rec in (("spans", w["spans"]), ("events", w["events"])):
+        mine = np.ascontiguousarray(rec[rank::world])
+        t = torch.from_numpy(mine.view(np.int64).reshape(len(mine), 4).copy())
+        got, src, idx = sharding.exchange(t, torch.from_numpy(owner[mine["ident"]]))
+        parts[name] = got.numpy().reshape(-1).view(rec.dtype)
+        parts[name + "_gidx"] = (idx.numpy() * world + src.numpy())     # position in the unsharded batch
+        assert (owner[parts[name]["ident"]] == rank).all()              # every record landed on its owner
+    from oracle import cpu as O
+    j = O.process_batch(parts["spans"], parts["events"], w["idents"], indexed=True)
+    np.savez(os.path.join(out_dir, "rank%d.npz" % rank), span_gidx=parts["spans_gidx"], event_gidx=parts["events_gidx"],
+             cand=j["cand_event"], low=np.array([j["debug"].low_confidence]))
+    dist.destroy_process_group()
+
+
+def test_all_to_all_exchange_of_unsharded_input(tmp_path):
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_exchange_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    w = synth.generate_host(synth.config(40_000, 4_000, 32, 8, 2, seed=9, horizon_ns=5_000_000_000))
+    from oracle import cpu as O
+    whole = O.process_batch(w["spans"], w["events"], w["idents"], indexed=True)
+    low, seen = 0, 0
+    for r in range(2):
+        z = np.load(os.path.join(str(tmp_path), "rank%d.npz" % r))
+        cand = np.where(z["cand"] == A.NONE, A.NONE, z["event_gidx"][np.minimum(z["cand"], len(z["event_gidx"]) - 1)]).astype(np.uint32)
+        assert np.array_equal(cand, whole["cand_event"][z["span_gidx"]])
+        low += int(z["low"][0])
+        seen += len(z["span_gidx"])
+    assert seen == 4_000 and low == whole["debug"].low_confidence
