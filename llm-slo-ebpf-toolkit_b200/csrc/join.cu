@@ -16,14 +16,13 @@
 //                  tiers 2-4 can be): two reads of the counting sort's bin table, or binary searches in the
 //                  sorted keys on the radix path.
 //   k_join_tiles   a CTA takes 128 consecutive spans.  Their ranges overlap heavily (each event is inside
-//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — six columns,
-//                  28 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier)
-//                  and its 8 warps scan their spans' windows out of shared memory, one warp per span:
-//                  a 128-bit vectorised pass over the trace|signal column of [a, b) (tier 1), the full
-//                  decision only over [a2, b2), candidates appended to a per-warp list by ballot
-//                  compaction, best `fanout` picked at the end with warp REDUX minima.
-//                  HBM/L2 traffic drops from ~11 KB to ~0.5 KB per span.  A span whose own range does
-//                  not fit a tile is scanned straight from global memory by the same code.
+//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — five columns,
+//                  24 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier).
+//                  Tier 1 is a tile-local hash join (every tile event probes a hash of the chunk's span trace
+//                  ids once); tiers 2-4 are decided by two threads per span walking the span's inner range
+//                  out of shared memory; matches are noted in two bytes and ordered afterwards in registers.
+//   k_join_big     the spans the tile kernel leaves out (range larger than a tile, overflowing note list, time
+//                  outside the events' range, fanout > 8): one warp per span straight from global memory.
 // Outputs are written at the span's input position; optionally the per-incident maxima (A7 glue) are
 // accumulated from the epilogue with one atomicMax per present attribute.
 #include <algorithm>

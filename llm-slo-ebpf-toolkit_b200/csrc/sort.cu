@@ -1,21 +1,25 @@
-// sort.cu — K-sort: stable LSD radix sort of events (and spans) by (join group, quantised time).
+// sort.cu — K-sort: events (and spans) grouped by (join group, quantised time).
 //
 // What the reference does here: nothing — ProcessBatch loops every span over every signal
-// (ebpfcorrelator/processor.go:29-49, correlator.go:72-90).  The sort is how this library reaches the
-// same match sets in O(E log E + S*w) instead of O(S*E).
+// (ebpfcorrelator/processor.go:29-49, correlator.go:72-90).  Grouping is how this library reaches the
+// same match sets in O(E + S*w) instead of O(S*E).
 //
-// Layout in HBM.  The 32-byte records are not moved during the passes: the passes permute
-// (key, index) pairs — 8 bytes per event when the key fits 32 bits, 12 otherwise — and one gather at
-// the end writes the records in key order.  Keys are (grp << tbits) | ((ts - ts_min) >> shift):
-// the join never needs a total order in time (it selects candidates by an explicit
-// (tier, |dt|, input index) order), only that a span's window is a contiguous range, so the time
-// quantum 2^shift is chosen as large as the window allows (<= window/64) and the key shrinks from
-// ~50 bits to 24-32: 3-4 radix passes instead of 6-7.  `exact` (lsg_sort_events_dev) uses shift 0.
+// Keys are (grp << tbits) | ((ts - ts_min) >> shift).  The join never needs a total order in time (it
+// selects candidates by an explicit (tier, |dt|, input index) order), only that a span's window is one
+// contiguous range, so the time quantum 2^shift is as large as the window allows (<= window/32) and the
+// key shrinks from ~50 bits to 23-30.  `exact` (lsg_sort_events_dev) uses shift 0.
 //
-// Each pass = per-tile digit histogram -> per-digit scan over tiles -> stable scatter.  Ranking inside
-// a tile is warp-synchronous (__match_any_sync, one shared-memory counter row per warp), items are
-// staged in shared memory in digit order so that the global writes are coalesced runs.  No
-// inter-CTA spin-waits: tiles only communicate through the scanned histogram.
+// Two ways to group, both ending in ONE gather that moves the 32-byte records (random reads, sequential
+// writes; random 32-byte writes measured 2.6x slower):
+//   counting sort  (key space <= 2^25, not exact)  one counter per key in an L2-resident table:
+//                  k_count_keys (key + rank by returning atomic) -> exclusive scan -> k_place_events
+//                  (permutation).  Order inside one key = whatever the atomics gave.
+//   LSD radix sort (larger key spaces, spans, the exact entry point)  stable; per pass: per-tile digit
+//                  histogram -> per-digit scan over tiles -> scatter of (key, index) pairs.  Ranking inside
+//                  a tile is warp-synchronous (peer masks from eight ballots, one shared-memory counter
+//                  row per warp, no atomics); items are staged in shared memory in digit order so that the
+//                  global writes are coalesced runs.  No inter-CTA spin-waits: tiles only communicate
+//                  through the scanned histogram.
 #include "common.cuh"
 
 namespace {

@@ -49,6 +49,7 @@ def test_random_string_batches_vs_string_oracle(ctx, seed):
 @pytest.mark.parametrize("window_ms,thr,fanout,horizon_s,n_pods,ppg", [
     (2000, 0.7, 3, 36, 64, 2), (2000, 0.7, 3, 3600, 64, 2), (100, 0.85, 1, 36, 16, 1), (5000, 0.6, 8, 20, 8, 4),
     (2000, 1.0, 2, 36, 64, 2), (250, 0.7, 5, 4, 4, 2), (2000, 0.6, 12, 36, 16, 2), (1000, 0.7, 32, 10, 8, 2),
+    (2000, 0.7, 3, 3600, 4096, 2),   # 2048 groups x 2^17 quanta: too many keys for the counting sort -> radix path
 ])
 def test_synthetic_vs_indexed_oracle(ctx, window_ms, thr, fanout, horizon_s, n_pods, ppg):
     cfg = synth.config(200_000, 20_000, n_pods, max(ppg, 8 if n_pods >= 8 else n_pods), ppg, seed=window_ms + fanout,
