@@ -141,7 +141,23 @@ def run_reference(args, out):
     n_events, n_spans = 200_000, 20_000
     cfg = sample_cfg(n_events, n_spans)
     w = synth.generate_host(cfg)
-    for _ in range(args.warmup):
+    t_probe = time.perf_counter()
+    cpu_pass(w, True, threads)                      # also the first warm-up step
+    t_probe = time.perf_counter() - t_probe
+    # keep the whole run within a few minutes whatever --steps is: the loop costs O(S x E), so shrink both sides
+    budget_s = 150.0
+    total_steps = max(args.steps + max(args.warmup - 1, 0), 1)
+    for _ in range(3):   # the cost is not exactly quadratic (fixed per-pass overheads): re-probe after shrinking
+        if t_probe * total_steps <= budget_s or n_spans <= 1_000:
+            break
+        scale = max((budget_s / (t_probe * total_steps)) ** 0.5 * 0.9, 0.05)
+        n_events, n_spans = max(int(n_events * scale), 10_000), max(int(n_spans * scale), 1_000)
+        cfg = sample_cfg(n_events, n_spans)
+        w = synth.generate_host(cfg)
+        t_probe = time.perf_counter()
+        cpu_pass(w, True, threads)
+        t_probe = time.perf_counter() - t_probe
+    for _ in range(max(args.warmup - 1, 0)):
         cpu_pass(w, True, threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
@@ -149,8 +165,8 @@ def run_reference(args, out):
     dt = time.perf_counter() - t0
     value = n_events * args.steps / dt
     sample = ("brute force O(S x E) as the reference's ProcessBatch, on %d events x %d spans with C2's per-pod density "
-              "(1/50 of C2); the loop's cost per event grows with S, so at full C2 (1M spans) the same code is ~50x "
-              "slower per event" % (n_events, n_spans))
+              "(1/%d of C2); the loop's cost per event grows with S, so at full C2 (1M spans) the same code is ~%dx "
+              "slower per event" % (n_events, n_spans, round(1_000_000 / n_spans), round(1_000_000 / n_spans)))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",

@@ -62,9 +62,7 @@ k_event_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *_
   long long tmin = INT64_MAX, tmax = INT64_MIN;
   unsigned int live = 0, unsup = 0;
   bool bad = false;
-#pragma unroll 4
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    EventRec e = load_event(events + i);
+  auto look = [&](const EventRec &e) {
     uint32_t g;
     if ((e.trace_sig & 15u) >= LSG_NSIG) unsup++;
     if (event_live(e, idents, n_idents, &g, &bad)) {
@@ -72,7 +70,18 @@ k_event_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *_
       tmin = min(tmin, (long long)e.ts);
       tmax = max(tmax, (long long)e.ts);
     }
+  };
+  // streaming read of every record: four 256-bit loads in flight per thread
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    EventRec e[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) e[u] = load_event(events + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) look(e[u]);
   }
+  for (; i < n; i += stride) look(load_event(events + i));
   for (int o = 16; o; o >>= 1) {
     tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
     tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
