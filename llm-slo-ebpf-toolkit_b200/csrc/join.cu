@@ -519,12 +519,14 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       const int k = i0 + (int)(tid >> 1);
       const unsigned h = tid & 1;
       const bool live = k < i1;
-      unsigned n_match = 0, n_low = 0;
+      unsigned n_match = 0, n_low = 0, n_unlisted = 0;
       SpanRec s;
       s.ts = 0; s.ident = 0; s.pid = 0; s.conn = 0; s.trace = 0; s.incident = LSG_NONE;
       if (live) {
         s = span_from_halves(sm.span[k][0], sm.span[k][1]);
         const uint4 rg = sm.rng[k];
+        // `fanout` trace-id matches (confidence 1.0) already noted: a tier 2-4 candidate can be counted but never kept
+        const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)p.fanout;
         if (rg.z < rg.w && rg.z != 0xffffffffu) {
           const lsg_ident sid = load_ident(p.idents, s.ident);
           const bool pod_ok = sid.pod != 0, svcnode_ok = sid.service != 0 && sid.node != 0;
@@ -562,8 +564,12 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             const bool low = m & (tier > cut);                                   // correlator.go:83-86
             n_low += low;
             if (m & !low) {
-              const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-              if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+              if (full) {
+                n_unlisted++;
+              } else {
+                const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+                if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+              }
             }
           }
         }
@@ -596,6 +602,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       }
       n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
       n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
+      n_unlisted += __shfl_down_sync(0xffffffffu, n_unlisted, 1);
+      n_cand += n_unlisted;   // candidates that were counted without being noted
       // ---- write: the even lane owns the span
       if (live && !h) {
         if (redo) {
