@@ -330,6 +330,19 @@ int lsg_retry_storm(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_i
 int lsg_retry_storm_dev(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                         int64_t window_ns, int threshold, uint32_t *count_out, uint8_t *storm_out);
 
+/* F4  lsg_segment_quantiles: quantile() of pkg/slo/calculator.go:121-149 (same body: pkg/releasegate/gate.go:737-760)
+ *     for many value lists in one call, e.g. one list per (scenario, phase, signal) for the `*_p95` / `*_p50`
+ *     assertions of test/incident-lab/scenarios/<name>.yaml, or per node for releasegate's node p95.  Record i belongs
+ *     to list segment[i]; ids >= n_segments are ignored; segment == NULL means one list (n_segments must be <= 1).
+ *     out[s * n_q + j] = quantile(list s, q[j]): 0 for an empty list, q clamped to [0, 1], a sorted copy with NaN
+ *     first (sort.Float64s), pos = q * (len - 1), linear interpolation between floor(pos) and ceil(pos) in the
+ *     reference's operation order.  count_out[s] (optional) = len(list s).  n < 2^32.  NaN in q is rejected by
+ *     the host variant.  The same kernels give the north star's "quantile sketch" feature an exact meaning. */
+int lsg_segment_quantiles(lsg_ctx *ctx, const double *values, const uint32_t *segment, size_t n, size_t n_segments,
+                          const double *q, size_t n_q, double *out /* n_segments * n_q */, uint64_t *count_out);
+int lsg_segment_quantiles_dev(lsg_ctx *ctx, const double *values, const uint32_t *segment, size_t n, size_t n_segments,
+                              const double *q, size_t n_q, double *out, uint64_t *count_out);
+
 /* ---- synthetic workload: record i is a pure function of (seed, i), generated on
  *      the device by lsg_synth_dev and on the host by lsg_synth_host with identical results. */
 typedef struct {

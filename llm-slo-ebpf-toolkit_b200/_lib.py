@@ -85,6 +85,8 @@ def load_library():
             getattr(lib, name).argtypes = [vp, vp, sz, vp]
         for name in ("lsg_retry_storm", "lsg_retry_storm_dev"):
             getattr(lib, name).argtypes = [vp, vp, sz, vp, sz, i64, cint, vp, vp]
+        for name in ("lsg_segment_quantiles", "lsg_segment_quantiles_dev"):
+            getattr(lib, name).argtypes = [vp, vp, vp, sz, sz, vp, sz, vp, vp]
         lib.lsg_incident_signals_static.argtypes = [vp, vp, vp, sz, sz, vp, C.c_char_p, sz]
         lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
         lib.lsg_abi_sizes.restype = cint
@@ -236,6 +238,18 @@ class Context:
         self._check(self._lib.lsg_retry_storm(self._h, _ptr(events), len(events), _ptr(idents), len(idents), int(window_ns),
                                               int(threshold), _ptr(cnt), _ptr(storm)))
         return cnt, storm
+
+    def segment_quantiles(self, values, segment, n_segments, q):
+        """quantile(list s, q[j]) for every list and q (calculator.go:121-149) -> (out[n_segments, n_q], counts)"""
+        values, q = _as(values, np.float64), _as(q, np.float64)
+        segment = _as(segment, np.uint32)
+        if segment is not None and len(segment) != len(values):
+            raise ValueError("segment and values differ in length")
+        out = np.zeros((int(n_segments), len(q)), np.float64)
+        cnt = np.zeros(int(n_segments), np.uint64)
+        self._check(self._lib.lsg_segment_quantiles(self._h, _ptr(values), _ptr(segment), len(values), int(n_segments),
+                                                    _ptr(q), len(q), _ptr(out), _ptr(cnt)))
+        return out, cnt
 
     def last_sort_info(self):
         b, sh, ps = C.c_uint32(), C.c_uint32(), C.c_uint32()

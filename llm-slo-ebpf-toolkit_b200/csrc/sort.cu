@@ -897,3 +897,173 @@ int lsg_sort_signal_by_pod(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
   *perm_out = perm;
   return 0;
 }
+
+// ---- F4: exact quantiles per segment -----------------------------------------------------------------------
+// quantile() of pkg/slo/calculator.go:121-149 (the same body as pkg/releasegate/gate.go:737-760) over many value
+// lists at once: a stable LSD sort by value, then by segment, leaves every segment's values contiguous and
+// ascending; one thread per (segment, q) then reads the two neighbours of pos = q * (count - 1).
+namespace {
+constexpr int QH_MAX = 4096;   // segment histograms up to this size are accumulated in shared memory first
+
+// sort.Float64s puts NaN before every number; f64_key() of a non-NaN is never 0
+__device__ __forceinline__ unsigned long long quant_key(double v) { return isnan(v) ? 0ull : f64_key(v); }
+
+__global__ void __launch_bounds__(256)
+k_quant_keys(const double *__restrict__ values, const uint32_t *__restrict__ seg, size_t n, uint32_t n_seg,
+             uint64_t *__restrict__ keys, uint32_t *__restrict__ counts) {
+  __shared__ uint32_t s_hist[QH_MAX];
+  const bool local = n_seg + 1 <= (uint32_t)QH_MAX;
+  if (local) {
+    for (uint32_t k = threadIdx.x; k <= n_seg; k += blockDim.x) s_hist[k] = 0;
+    __syncthreads();
+  }
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    keys[i] = quant_key(values[i]);
+    uint32_t s = seg ? seg[i] : 0u;
+    if (s > n_seg) s = n_seg;             // out-of-range segment ids share one trailing bucket that nobody reads
+    atomicAdd(local ? &s_hist[s] : &counts[s], 1u);
+  }
+  if (local) {
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k <= n_seg; k += blockDim.x)
+      if (s_hist[k]) atomicAdd(&counts[k], s_hist[k]);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_quant_segkeys(const uint32_t *__restrict__ seg, const uint32_t *__restrict__ perm, size_t n, uint32_t n_seg,
+                uint32_t *__restrict__ segkeys) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    segkeys[i] = min(seg[perm[i]], n_seg);
+}
+
+// offsets[s] = start of segment s in the final order (exclusive scan of the counts); by_value = keys after the
+// value sort; perm2 (NULL = identity) maps a final position to a position of by_value
+__global__ void __launch_bounds__(256)
+k_quant_pick(const uint64_t *__restrict__ by_value, const uint32_t *__restrict__ perm2, const uint32_t *__restrict__ offsets,
+             uint32_t n_seg, const double *__restrict__ q, uint32_t n_q, double *__restrict__ out,
+             uint64_t *__restrict__ count_out) {
+  const size_t total = (size_t)n_seg * n_q;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t s = (uint32_t)(t / n_q), j = (uint32_t)(t % n_q);
+    const uint32_t off = offsets[s], cnt = offsets[s + 1] - off;
+    if (j == 0 && count_out) count_out[s] = cnt;
+    if (!out) continue;                                      // counts only
+    double r = 0.0;                                          // calculator.go:122-124
+    if (cnt) {
+      double qq = q[j];
+      if (qq <= 0) qq = 0;                                   // calculator.go:125-130
+      if (qq >= 1) qq = 1;
+      auto at = [&](uint32_t k) { const uint32_t p = off + k; return key_f64(by_value[perm2 ? perm2[p] : p]); };
+      if (cnt == 1) {
+        r = at(0);                                           // calculator.go:136-138
+      } else {
+        const double pos = qq * (double)(cnt - 1);           // calculator.go:140-148
+        const double lo = floor(pos), hi = ceil(pos);
+        if (lo == hi) {
+          r = at((uint32_t)lo);
+        } else {
+          const double frac = pos - lo;
+          r = at((uint32_t)lo) * (1 - frac) + at((uint32_t)hi) * frac;
+        }
+      }
+    }
+    out[t] = r;
+  }
+}
+
+template <typename T>
+int quant_stage(lsg_ctx *ctx, int slot, const T *host, size_t n, const T **dev) {
+  *dev = nullptr;
+  if (!host) return 0;
+  void *p;
+  LSG_TRY(lsg_ws(ctx, slot, n * sizeof(T), &p));
+  if (n) LSG_CUDA(ctx, cudaMemcpyAsync(p, host, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+  *dev = (const T *)p;
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int lsg_segment_quantiles_dev(lsg_ctx *ctx, const double *values, const uint32_t *segment, size_t n, size_t n_segments,
+                              const double *q, size_t n_q, double *out, uint64_t *count_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n && !values) || (n_q && !q) || (n_segments && n_q && !out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n %zu does not fit 32-bit indices", n);
+  if (n_segments >= ((size_t)1 << 31)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_segments %zu is out of range", n_segments);
+  if (n && !segment && n_segments > 1) return lsg_fail(ctx, LSG_ERR_INVALID, "segment is NULL but n_segments is %zu", n_segments);
+  LSG_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (n_segments == 0 || (n_q == 0 && !count_out)) return 0;
+  const uint32_t n_seg = (uint32_t)n_segments;
+  // counts[0..n_seg] (+ one trailing zero so that the scan yields n_seg + 2 offsets)
+  const size_t n_cnt = (size_t)n_seg + 2;
+  const uint32_t n_blocks = (uint32_t)((n_cnt + SCAN_TILE - 1) / SCAN_TILE);
+  void *cnt_v, *sums_v;
+  LSG_TRY(lsg_ws(ctx, WS_BINS, n_cnt * 4 + 64, &cnt_v));
+  LSG_TRY(lsg_ws(ctx, WS_SCAN, (size_t)n_blocks * 4 + 64, &sums_v));
+  uint32_t *counts = (uint32_t *)cnt_v;
+  LSG_CUDA(ctx, cudaMemsetAsync(counts, 0, n_cnt * 4, ctx->stream));
+  uint64_t *by_value = nullptr;
+  uint32_t *perm2 = nullptr;
+  if (n) {
+    void *ka, *kb, *ia, *ib;
+    LSG_TRY(lsg_ws(ctx, WS_KEYS_A, n * 8, &ka));
+    LSG_TRY(lsg_ws(ctx, WS_KEYS_B, n * 8, &kb));
+    LSG_TRY(lsg_ws(ctx, WS_IDX_A, n * 4 + 64, &ia));
+    LSG_TRY(lsg_ws(ctx, WS_IDX_B, n * 4 + 64, &ib));
+    k_quant_keys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(values, segment, n, n_seg, (uint64_t *)ka, counts);
+    LSG_LAUNCH_CHECK(ctx);
+    uint32_t *perm1;
+    LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, 64, WS_HIST,
+                                       &by_value, &perm1));
+    if (segment) {   // a stable second sort by segment keeps each segment's values ascending
+      void *sa, *sb, *ja, *jb;
+      LSG_TRY(lsg_ws(ctx, WS_SPAN_KEYS_A, n * 4 + 64, &sa));
+      LSG_TRY(lsg_ws(ctx, WS_SPAN_KEYS_B, n * 4 + 64, &sb));
+      LSG_TRY(lsg_ws(ctx, WS_SPAN_IDX_A, n * 4 + 64, &ja));
+      LSG_TRY(lsg_ws(ctx, WS_SPAN_IDX_B, n * 4 + 64, &jb));
+      k_quant_segkeys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(segment, perm1, n, n_seg, (uint32_t *)sa);
+      LSG_LAUNCH_CHECK(ctx);
+      uint32_t *seg_sorted;
+      LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)sa, (uint32_t *)sb, (uint32_t *)ja, (uint32_t *)jb, n,
+                                         bits_of(n_seg), WS_SPAN_HIST, &seg_sorted, &perm2));
+    }
+  }
+  k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(counts, n_cnt, (uint32_t *)sums_v);
+  LSG_LAUNCH_CHECK(ctx);
+  k_scan_sums<<<1, 1024, 0, ctx->stream>>>((uint32_t *)sums_v, n_blocks);
+  LSG_LAUNCH_CHECK(ctx);
+  k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(counts, n_cnt, (uint32_t *)sums_v);
+  LSG_LAUNCH_CHECK(ctx);
+  const uint32_t nq_eff = n_q ? (uint32_t)n_q : 1u;   // n_q == 0: one thread per segment writes count_out only
+  k_quant_pick<<<grid_for(ctx, (size_t)n_seg * nq_eff, 256, 8), 256, 0, ctx->stream>>>(by_value, perm2, counts, n_seg, q, nq_eff,
+                                                                                      n_q ? out : nullptr, count_out);
+  LSG_LAUNCH_CHECK(ctx);
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int lsg_segment_quantiles(lsg_ctx *ctx, const double *values, const uint32_t *segment, size_t n, size_t n_segments,
+                          const double *q, size_t n_q, double *out, uint64_t *count_out) {
+  if (!ctx) return LSG_ERR_INVALID;
+  if ((n && !values) || (n_q && !q) || (n_segments && n_q && !out)) return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
+  for (size_t j = 0; j < n_q; ++j)
+    if (q[j] != q[j]) return lsg_fail(ctx, LSG_ERR_INVALID, "q[%zu] is NaN", j);
+  LSG_CUDA(ctx, cudaSetDevice(ctx->device));
+  const double *d_val, *d_q;
+  const uint32_t *d_seg;
+  LSG_TRY(quant_stage(ctx, WS_IN0, values, n, &d_val));
+  LSG_TRY(quant_stage(ctx, WS_IN1, segment, n, &d_seg));
+  LSG_TRY(quant_stage(ctx, WS_IN2, q, n_q, &d_q));
+  void *d_out = nullptr, *d_cnt = nullptr;
+  if (n_q) LSG_TRY(lsg_ws(ctx, WS_OUT0, n_segments * n_q * 8 + 8, &d_out));
+  if (count_out) LSG_TRY(lsg_ws(ctx, WS_OUT1, n_segments * 8 + 8, &d_cnt));
+  LSG_TRY(lsg_segment_quantiles_dev(ctx, d_val, d_seg, n, n_segments, d_q, n_q, (double *)d_out, (uint64_t *)d_cnt));
+  if (n_segments && n_q) LSG_CUDA(ctx, cudaMemcpyAsync(out, d_out, n_segments * n_q * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (n_segments && count_out) LSG_CUDA(ctx, cudaMemcpyAsync(count_out, d_cnt, n_segments * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -167,6 +167,23 @@ static void TestPipeline() {   // pipeline_test.go:46-175
   CHECK(at::BuildAttributions({sample("dns_latency")}, " RULE ")[0].PredictedFaultDomain == "network_dns");
 }
 
+// pkg/slo/calculator_test.go:34-52 (TestAggregate) + quantile edge cases of calculator.go:121-149
+static void TestAggregate() {
+  namespace sl = llmslo::slo;
+  std::vector<sl::Snapshot> items = {{100, 50, {20, 10, 5}}, {200, 30, {40, 15, 10}}, {300, 10, {60, 25, 15}}};
+  const auto out = sl::Aggregate(items);
+  CHECK(out.TTFTP50 == 200);
+  CHECK(out.TokensPerSP50 == 30);
+  CHECK(out.RetrievalP95MS > 0);
+  const double frac = 0.95 * 2.0 - 1.0;
+  CHECK(out.RetrievalP95MS == 65.0 * (1 - frac) + 100.0 * frac);
+  CHECK(sl::quantile({}, 0.5) == 0);
+  CHECK(sl::quantile({7.0}, 0.99) == 7.0);
+  CHECK(sl::quantile({3.0, 1.0, 2.0}, -1) == 1.0);
+  CHECK(sl::quantile({3.0, 1.0, 2.0}, 5) == 3.0);
+  CHECK(sl::Aggregate({}).TTFTP95 == 0);
+}
+
 int main() {
   try {
     TestMatchTiers();
@@ -174,6 +191,7 @@ int main() {
     TestCorrelator();
     TestBayesian();
     TestPipeline();
+    TestAggregate();
   } catch (const std::exception &e) {
     printf("EXCEPTION %s\n", e.what());
     return 2;

@@ -648,4 +648,36 @@ inline double CoverageAccuracy(const std::vector<FaultSample> &samples, const st
 }
 
 }  // namespace attribution
+
+// ---- pkg/slo: distribution summaries --------------------------------------------------
+namespace slo {
+struct Percentiles { double TTFTP50 = 0, TTFTP95 = 0, TTFTP99 = 0, TokensPerSP50 = 0, TokensPerSP95 = 0, RetrievalP95MS = 0; };   // calculator.go:32-40
+struct RetrievalBreakdown { double VectorDBMS = 0, NetworkMS = 0, DNSMS = 0; };
+struct Snapshot { double TTFTMs = 0, TokensPerS = 0; RetrievalBreakdown Retrieval; };
+
+// calculator.go:121-149
+inline double quantile(const std::vector<double> &values, double q) {
+  double out = 0;
+  Context::check(lsg_segment_quantiles(Context::get(), values.data(), nullptr, values.size(), 1, &q, 1, &out, nullptr));
+  return out;
+}
+inline double nonNegative(double v) { return v < 0 ? 0 : v; }   // calculator.go:151-156
+// calculator.go:90-93: negative components count as 0
+inline double TotalRetrievalMS(const RetrievalBreakdown &r) { return nonNegative(r.VectorDBMS) + nonNegative(r.NetworkMS) + nonNegative(r.DNSMS); }
+// calculator.go:99-118: the three value lists go down as three segments of one call
+inline Percentiles Aggregate(const std::vector<Snapshot> &items) {
+  if (items.empty()) return Percentiles{};   // calculator.go:96-98
+  std::vector<double> v;
+  std::vector<uint32_t> seg;
+  for (uint32_t k = 0; k < 3; ++k)
+    for (auto &it : items) {
+      v.push_back(k == 0 ? nonNegative(it.TTFTMs) : k == 1 ? nonNegative(it.TokensPerS) : TotalRetrievalMS(it.Retrieval));
+      seg.push_back(k);
+    }
+  const double q[3] = {0.50, 0.95, 0.99};
+  double out[9] = {};
+  Context::check(lsg_segment_quantiles(Context::get(), v.data(), seg.data(), v.size(), 3, q, 3, out, nullptr));
+  return Percentiles{out[0], out[1], out[2], out[3], out[4], out[7]};
+}
+}  // namespace slo
 }  // namespace llmslo

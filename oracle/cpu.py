@@ -40,6 +40,8 @@ def lib():
         L.orc_confusion.argtypes = [vp, vp, vp, vp, vp, dbl, dbl, sz, C.POINTER(A.ConfusionOut)]
         L.orc_confusion.restype = None
         L.orc_retry_storm.argtypes = [vp, vp, sz, C.c_uint32, i64, cint, vp, vp]
+        L.orc_segment_quantiles.argtypes = [vp, vp, sz, sz, vp, sz, vp, vp]
+        L.orc_segment_quantiles.restype = None
         L.orc_retry_storm.restype = None
         L.orc_hw_threads.restype = cint
         _LIB = L
@@ -120,6 +122,15 @@ def retry_storm(pod, ts, n_pods, window_ns, threshold):
     cnt, storm = np.empty(len(pod), np.uint32), np.empty(len(pod), np.uint8)
     lib().orc_retry_storm(_p(pod), _p(ts), len(pod), int(n_pods), int(window_ns), int(threshold), _p(cnt), _p(storm))
     return cnt, storm
+
+
+def segment_quantiles(values, segment, n_segments, q):
+    values, q = _c(values, np.float64), _c(q, np.float64)
+    segment = None if segment is None else _c(segment, np.uint32)
+    out, cnt = np.zeros((n_segments, len(q)), np.float64), np.zeros(n_segments, np.uint64)
+    lib().orc_segment_quantiles(_p(values), None if segment is None else _p(segment), len(values), int(n_segments), _p(q),
+                                len(q), _p(out), _p(cnt))
+    return out, cnt
 
 
 def hw_threads():

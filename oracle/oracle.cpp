@@ -444,6 +444,44 @@ void orc_retry_storm(const uint32_t *pod, const int64_t *ts, size_t n, uint32_t 
   }
 }
 
+// quantile(), pkg/slo/calculator.go:121-149 (same body pkg/releasegate/gate.go:737-760), per segment.
+// sort.Float64s orders NaN before every number; ids >= n_segments are skipped.
+void orc_segment_quantiles(const double *values, const uint32_t *segment, size_t n, size_t n_segments, const double *q,
+                           size_t n_q, double *out, uint64_t *count_out) {
+  std::vector<std::vector<double>> lists(n_segments);
+  for (size_t i = 0; i < n; ++i) {
+    const uint32_t s = segment ? segment[i] : 0u;
+    if (s < n_segments) lists[s].push_back(values[i]);
+  }
+  for (size_t s = 0; s < n_segments; ++s) {
+    auto &sorted = lists[s];
+    std::stable_sort(sorted.begin(), sorted.end(), [](double a, double b) { return a < b || (a != a && b == b); });
+    if (count_out) count_out[s] = sorted.size();
+    for (size_t j = 0; j < n_q; ++j) {
+      double qq = q[j], r;
+      if (sorted.empty()) {
+        r = 0;
+      } else {
+        if (qq <= 0) qq = 0;
+        if (qq >= 1) qq = 1;
+        if (sorted.size() == 1) {
+          r = sorted[0];
+        } else {
+          const double pos = qq * (double)(sorted.size() - 1);
+          const long lower = (long)std::floor(pos), upper = (long)std::ceil(pos);
+          if (lower == upper) {
+            r = sorted[lower];
+          } else {
+            const double frac = pos - (double)lower;
+            r = sorted[lower] * (1 - frac) + sorted[upper] * frac;
+          }
+        }
+      }
+      out[s * n_q + j] = r;
+    }
+  }
+}
+
 int orc_hw_threads(void) { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

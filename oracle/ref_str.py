@@ -684,3 +684,26 @@ def CoverageAccuracy(samples, predictions, threshold: float) -> float:
     if count == 0:
         return 0.0
     return total / float(count)
+
+
+# --------------------------------------------------------------------------------------------------
+# pkg/slo/calculator.go (quantile; pkg/releasegate/gate.go:737-760 has the same body)
+def quantile(values, q: float) -> float:
+    """calculator.go:121-149"""
+    if len(values) == 0:
+        return 0.0
+    if q <= 0:
+        q = 0.0
+    if q >= 1:
+        q = 1.0
+    # sort.Float64s: ascending, NaN first
+    sorted_ = sorted(values, key=lambda v: (0, 0.0) if v != v else (1, v))
+    if len(sorted_) == 1:
+        return sorted_[0]
+    pos = q * float(len(sorted_) - 1)
+    lower = int(math.floor(pos))
+    upper = int(math.ceil(pos))
+    if lower == upper:
+        return sorted_[lower]
+    frac = pos - float(lower)
+    return sorted_[lower] * (1 - frac) + sorted_[upper] * frac
