@@ -146,6 +146,14 @@ uint64_t lsg_launch_count(const lsg_ctx *ctx);
 /* bytes of device workspace currently held */
 size_t lsg_workspace_bytes(const lsg_ctx *ctx);
 
+/* Page-locked host memory for the buffers handed to the host entry points (lsg_pipeline, lsg_pipeline_submit,
+ * lsg_process_batch ...): copies from pageable memory are staged by the driver and cannot overlap.  write_combined
+ * != 0 asks for write-combining memory (cudaHostAllocWriteCombined): faster for the device to read on some hosts,
+ * very slow for the CPU to read back, so only for input buffers the host fills once and never reads.  Free with
+ * lsg_host_free.  No reference counterpart (Go slices are pageable); pkg/gpu would keep these as its staging. */
+int lsg_host_alloc(size_t bytes, int write_combined, void **out);
+void lsg_host_free(void *p);
+
 /* sizeof() of the ABI structs as compiled into the library, in header order (event, span, ident, debug, eval,
  * model, confusion_out, feature, counters, pipeline_args, synth_cfg); returns how many there are.  Lets a
  * binding check its own struct mirrors at load time. */

@@ -88,6 +88,9 @@ def load_library():
         for name in ("lsg_segment_quantiles", "lsg_segment_quantiles_dev"):
             getattr(lib, name).argtypes = [vp, vp, vp, sz, sz, vp, sz, vp, vp]
         lib.lsg_incident_signals_static.argtypes = [vp, vp, vp, sz, sz, vp, C.c_char_p, sz]
+        lib.lsg_host_alloc.argtypes = [sz, cint, P(vp)]
+        lib.lsg_host_free.argtypes = [vp]
+        lib.lsg_host_free.restype = None
         lib.lsg_abi_sizes.argtypes = [P(C.c_size_t), cint]
         lib.lsg_abi_sizes.restype = cint
         _LIB = lib
@@ -274,6 +277,38 @@ class Context:
 
 
 _DEFAULT = None
+
+
+class HostBuffer:
+    """Page-locked host memory from lsg_host_alloc, viewed as a numpy uint8 array (`.array`); `.ptr` is its address."""
+
+    def __init__(self, nbytes, write_combined=False):
+        self._lib = load_library()
+        p = C.c_void_p()
+        rc = self._lib.lsg_host_alloc(max(int(nbytes), 1), 1 if write_combined else 0, C.byref(p))
+        if rc != 0 or not p.value:
+            raise LsgError(rc, "lsg_host_alloc(%d bytes) failed" % nbytes)
+        self.ptr = p.value
+        self.nbytes = int(nbytes)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr))[: self.nbytes]
+
+    def fill_from(self, src):
+        """copy the bytes of a contiguous numpy array into the buffer (sequential writes: fine for write-combined memory)"""
+        b = np.ascontiguousarray(src).view(np.uint8).reshape(-1)
+        assert b.size <= self.nbytes
+        self.array[: b.size] = b
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self._lib.lsg_host_free(self.ptr)
+            self.ptr = 0
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 def default_context():

@@ -302,6 +302,22 @@ int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_sh
 
 const char *lsg_last_error(const lsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 uint64_t lsg_launch_count(const lsg_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int lsg_host_alloc(size_t bytes, int write_combined, void **out) {
+  if (!out) return LSG_ERR_INVALID;
+  *out = nullptr;
+  const cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *out = nullptr;
+    return e == cudaErrorMemoryAllocation ? LSG_ERR_NOMEM : LSG_ERR_CUDA;
+  }
+  return 0;
+}
+
+void lsg_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
 size_t lsg_workspace_bytes(const lsg_ctx *ctx) {
   size_t t = 0;
   if (ctx) for (int i = 0; i < WS_COUNT; ++i) t += ctx->ws_cap[i];
