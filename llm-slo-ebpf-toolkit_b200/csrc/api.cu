@@ -118,12 +118,14 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted));
   // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
+  const uint2 *ident_pc = nullptr;
   {
     LSG_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
     LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0));
     cudaStream_t main_stream = ctx->stream;
     ctx->stream = ctx->side;
-    const int rc = lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm);
+    int rc = lsg_ident_classes(ctx, idents, n_idents, &ident_pc);
+    if (!rc) rc = lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm);
     ctx->stream = main_stream;
     if (rc) return rc;
     LSG_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->side));
@@ -140,6 +142,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   ja.conf_out = conf_out; ja.retrieval_out = retrieval_out; ja.n_cand_out = n_cand_out;
   ja.counters = (uint64_t *)((char *)small_v + SMALL_JOIN);
   ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
+  ja.ident_pc = ident_pc;
   LSG_TRY(lsg_launch_join(ctx, ja));
   *join_counters_dev = ja.counters;
   return 0;

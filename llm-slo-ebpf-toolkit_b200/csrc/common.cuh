@@ -43,6 +43,8 @@ enum {
   WS_SPAN_HIST,      // radix sort of the spans: per-tile digit histograms
   WS_BINS,           // counting sort: one counter per key
   WS_SCAN,           // counting sort: block sums of the scan
+  WS_IDENT_PC,       // join: (pod, service+node class) per identity row
+  WS_IDENT_TABLE,    // join: hash table that numbers the (service, node) classes
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
   WS_PIPE_END = WS_PIPE + 2 * 14 - 1,
   WS_COUNT
@@ -287,8 +289,12 @@ struct JoinArgs {
   uint64_t *counters;  // device: [0] matched pairs, [1] low_confidence, [2] fanout_dropped, [3] candidates, [4] kept
   // optional fusion of the A7 glue: per (incident, signal) max keys updated straight from the join's epilogue
   unsigned long long *inc_keys; size_t n_incidents;
+  const uint2 *ident_pc;   // lsg_ident_classes() of `idents`, or NULL: lsg_launch_join computes it
 };
 int lsg_launch_join(lsg_ctx *, const JoinArgs &);
+// per identity row: x = pod id, y = class of its (service, node) pair (0 when either is empty; equal pairs get
+// equal classes), so that the join compares two words per (span, event) pair instead of loading identity rows
+int lsg_ident_classes(lsg_ctx *, const lsg_ident *idents, size_t n_idents, const uint2 **out);
 int lsg_launch_incident_finish(lsg_ctx *, const unsigned long long *keys, size_t n_incidents, double *signals_out);
 int lsg_launch_incident_features(lsg_ctx *, const double *span_attr, const uint32_t *span_incident, const lsg_span *spans,
                                  size_t n_spans, size_t n_incidents, double *signals_out, lsg_feature *features_out);

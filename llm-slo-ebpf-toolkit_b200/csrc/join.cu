@@ -45,6 +45,7 @@ struct JoinParams {
   const uint32_t *ev_perm;   // sorted position -> input index
   const uint4 *ranges;       // per span in key order: outer [x, y) and inner [z, w) in sorted positions
   const lsg_ident *idents;
+  const uint2 *ident_pc;     // per identity row: (pod, service+node class)
   uint32_t n_idents;
   int64_t window_ns;
   double threshold;
@@ -357,7 +358,7 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
 // A match is only noted — two bytes (tier, tile offset) in the span's list — and the lists are ordered
 // afterwards in registers, when every lane is doing the same thing.  A span whose list overflows (or whose range
 // does not fit a tile) is left to k_join_big.
-constexpr int TM_CAP = 1920;    // events per tile
+constexpr int TM_CAP = 1792;    // events per tile (28 B each; three CTAs per SM)
 constexpr int TM_LIST = 48;     // noted candidates per span
 constexpr int TM_MAX_F = 8;      // largest fanout the tile kernel keeps in registers
 constexpr int TM_HASH = 256;    // hash slots for the chunk's span trace ids (<= 128 keys)
@@ -387,7 +388,8 @@ struct TopF {
 
 struct TileSmem {
   int64_t ts[TM_CAP];
-  uint32_t ident[TM_CAP];
+  uint32_t pod[TM_CAP];             // staged as the identity row, rewritten in place to the row's pod id
+  uint32_t cls[TM_CAP];             // the row's (service, node) class
   uint32_t pid[TM_CAP];
   uint32_t conn[TM_CAP];
   uint32_t trsig[TM_CAP];
@@ -480,7 +482,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           mbar_expect_tx(&sm.bar, count * 24u);
           bulk_g2s(sm.ts, p.ev.ts + A, count * 8u, &sm.bar);
           bulk_g2s(sm.trsig, p.ev.trsig + A, count * 4u, &sm.bar);
-          bulk_g2s(sm.ident, p.ev.ident + A, count * 4u, &sm.bar);
+          bulk_g2s(sm.pod, p.ev.ident + A, count * 4u, &sm.bar);
           bulk_g2s(sm.pid, p.ev.pid + A, count * 4u, &sm.bar);
           bulk_g2s(sm.conn, p.ev.conn + A, count * 4u, &sm.bar);
         }
@@ -489,6 +491,13 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       if (count) {
         mbar_wait(&sm.bar, phase);
         phase ^= 1;
+        // identity row -> (pod, class), once per staged event instead of once per (span, event) pair
+        for (uint32_t o = tid; o < count; o += JT_THREADS) {
+          const uint32_t row = sm.pod[o];
+          const uint2 pc = row < p.n_idents ? __ldg(p.ident_pc + row) : make_uint2(0u, 0u);   // padding past the last event
+          sm.pod[o] = pc.x;
+          sm.cls[o] = pc.y;
+        }
       }
       __syncthreads();
       // ---- tier 1: every event of the tile probes the hash once
@@ -528,8 +537,10 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         // `fanout` trace-id matches (confidence 1.0) already noted: a tier 2-4 candidate can be counted but never kept
         const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)p.fanout;
         if (rg.z < rg.w && rg.z != 0xffffffffu) {
-          const lsg_ident sid = load_ident(p.idents, s.ident);
-          const bool pod_ok = sid.pod != 0, svcnode_ok = sid.service != 0 && sid.node != 0;
+          const uint2 spc = __ldg(p.ident_pc + s.ident);
+          // an empty pod / service / node never matches (dns.go:61-73); classes are <= n_idents, so ~0 is no event's class
+          const bool pod_ok = spc.x != 0;
+          const uint32_t s_pod = spc.x, s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
           const bool pid_ok = s.pid != 0, conn_ok = s.conn != 0;
           const uint32_t zo = rg.z - A, wo = rg.w - A;
           const uint32_t mid = zo + ((wo - zo) >> 1);
@@ -539,7 +550,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;       // event trace ids are < 2^28
           for (uint32_t o = beg; o < end; ++o) {
             // every operand is loaded up front (five independent shared-memory loads), the decision is predicate arithmetic
-            const uint32_t e_trsig = sm.trsig[o], e_ident = sm.ident[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
+            const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_cls = sm.cls[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
             bool in, in100, in250;
             if (T32) {   // |dt| < 2^31 ns for every event of an inner range: 32-bit arithmetic is exact
               const int32_t d = (int32_t)(ts_lo[2 * o] - s_lo);
@@ -549,12 +560,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
               const uint64_t ad = lsg_absdiff(s.ts, sm.ts[o]);
               in = ad <= Wi; in100 = ad <= (uint64_t)(100 * kMs); in250 = ad <= (uint64_t)(250 * kMs);
             }
-            bool same_pod = pod_ok, same_sn = svcnode_ok;
-            if (e_ident != s.ident) {   // another identity row: compare the interned strings
-              const lsg_ident eid = load_ident(p.idents, e_ident);
-              same_pod = pod_ok && sid.pod == eid.pod;
-              same_sn = svcnode_ok && sid.service == eid.service && sid.node == eid.node;
-            }
+            const bool same_pod = pod_ok & (e_pod == s_pod), same_sn = e_cls == s_cls;
             const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
             const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
             const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
@@ -721,7 +727,71 @@ k_join_big(const __grid_constant__ JoinParams p, const uint32_t *__restrict__ bi
   if (tid < 5 && s_cnt[tid]) atomicAdd(&p.counters[tid], s_cnt[tid]);
 }
 
+// ---- (pod, class) per identity row -------------------------------------------------------------------
+// Rows with the same non-empty (service, node) pair get the same class: 1 + the smallest row index that carries
+// the pair, found through an open-addressing table keyed by the pair.
+__device__ __forceinline__ uint32_t pair_slot(uint64_t key, uint32_t mask) {
+  key ^= key >> 33; key *= 0xff51afd7ed558ccdull; key ^= key >> 33;
+  return (uint32_t)key & mask;
+}
+
+__global__ void __launch_bounds__(256)
+k_ident_class_insert(const lsg_ident *__restrict__ idents, uint32_t n, unsigned long long *__restrict__ tkey,
+                     uint32_t *__restrict__ tmin, uint32_t mask) {
+  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
+    const lsg_ident id = load_ident(idents, r);
+    if (id.service == 0 || id.node == 0) continue;
+    const unsigned long long key = ((unsigned long long)id.service << 32) | id.node;   // non-zero
+    uint32_t slot = pair_slot(key, mask);
+    for (;;) {
+      const unsigned long long prev = atomicCAS(&tkey[slot], 0ull, key);
+      if (prev == 0ull || prev == key) break;
+      slot = (slot + 1) & mask;
+    }
+    atomicMin(&tmin[slot], r);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_ident_class_emit(const lsg_ident *__restrict__ idents, uint32_t n, const unsigned long long *__restrict__ tkey,
+                   const uint32_t *__restrict__ tmin, uint32_t mask, uint2 *__restrict__ pc) {
+  for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x) {
+    const lsg_ident id = load_ident(idents, r);
+    uint32_t cls = 0;
+    if (id.service != 0 && id.node != 0) {
+      const unsigned long long key = ((unsigned long long)id.service << 32) | id.node;
+      uint32_t slot = pair_slot(key, mask);
+      while (tkey[slot] != key) slot = (slot + 1) & mask;
+      cls = tmin[slot] + 1u;
+    }
+    pc[r] = make_uint2(id.pod, cls);
+  }
+}
+
 }  // namespace
+
+int lsg_ident_classes(lsg_ctx *ctx, const lsg_ident *idents, size_t n_idents, const uint2 **out) {
+  *out = nullptr;
+  if (n_idents >= ((size_t)1 << 31)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_idents %zu is out of range", n_idents);
+  size_t cap = 64;
+  while (cap < 2 * n_idents) cap <<= 1;
+  void *pv, *tv;
+  LSG_TRY(lsg_ws(ctx, WS_IDENT_PC, (n_idents + 1) * sizeof(uint2), &pv));
+  LSG_TRY(lsg_ws(ctx, WS_IDENT_TABLE, cap * 12, &tv));
+  *out = (const uint2 *)pv;
+  if (n_idents == 0) return 0;
+  unsigned long long *tkey = (unsigned long long *)tv;
+  uint32_t *tmin = (uint32_t *)((char *)tv + cap * 8);
+  LSG_CUDA(ctx, cudaMemsetAsync(tkey, 0, cap * 8, ctx->stream));
+  LSG_CUDA(ctx, cudaMemsetAsync(tmin, 0xff, cap * 4, ctx->stream));
+  size_t blocks = (n_idents + 255) / 256, lim = (size_t)ctx->sm_count * 8;
+  if (blocks > lim) blocks = lim;
+  k_ident_class_insert<<<(unsigned)blocks, 256, 0, ctx->stream>>>(idents, (uint32_t)n_idents, tkey, tmin, (uint32_t)cap - 1);
+  LSG_LAUNCH_CHECK(ctx);
+  k_ident_class_emit<<<(unsigned)blocks, 256, 0, ctx->stream>>>(idents, (uint32_t)n_idents, tkey, tmin, (uint32_t)cap - 1, (uint2 *)pv);
+  LSG_LAUNCH_CHECK(ctx);
+  return 0;
+}
 
 int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   LSG_CUDA(ctx, cudaMemsetAsync(a.counters, 0, 8 * sizeof(uint64_t), ctx->stream));
@@ -747,6 +817,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   p.spans = a.spans; p.span_perm = a.span_perm; p.n_spans = a.n_spans;
   p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv;
   p.idents = a.idents; p.n_idents = (uint32_t)a.n_idents;
+  p.ident_pc = a.ident_pc;
+  if (!p.ident_pc) LSG_TRY(lsg_ident_classes(ctx, a.idents, a.n_idents, &p.ident_pc));
   p.window_ns = a.window_ns; p.threshold = a.threshold; p.fanout = a.fanout;
   p.attr_base = a.attr_base; p.cand_event = a.cand_event; p.cand_tier = a.cand_tier; p.attr_out = a.attr_out;
   p.conf_out = a.conf_out; p.retrieval_out = a.retrieval_out; p.n_cand_out = a.n_cand_out;
