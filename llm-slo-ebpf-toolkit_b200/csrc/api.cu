@@ -115,7 +115,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
                        double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
                        unsigned long long *inc_keys = nullptr, size_t n_incidents = 0) {
-  LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted));
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans));
   // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
   const uint2 *ident_pc = nullptr;
@@ -203,33 +203,28 @@ int lsg_create(int device, void *stream, lsg_ctx **out) {
   lsg_ctx *ctx = new (std::nothrow) lsg_ctx();
   if (!ctx) return LSG_ERR_NOMEM;
   ctx->device = device;
-  if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return LSG_ERR_NODEVICE; }
+  auto fail = [&](int code) {   // lsg_destroy releases whatever exists so far
+    cudaGetLastError();
+    lsg_destroy(ctx);
+    return code;
+  };
+  if (cudaSetDevice(device) != cudaSuccess) return fail(LSG_ERR_NODEVICE);
   cudaDeviceProp prop;
-  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return LSG_ERR_NODEVICE; }
-  if (prop.major < 10) {   // the kernels are built for sm_100a only
-    delete ctx;
-    return LSG_ERR_NODEVICE;
-  }
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(LSG_ERR_NODEVICE);
+  if (prop.major < 10) return fail(LSG_ERR_NODEVICE);   // the kernels are built for sm_100a only
   ctx->sm_count = prop.multiProcessorCount;
   if (stream) {
     ctx->stream = (cudaStream_t)stream;
   } else {
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return LSG_ERR_CUDA; }
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(LSG_ERR_CUDA);
     ctx->own_stream = true;
   }
   if (cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess) {
-    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
-    delete ctx;
-    return LSG_ERR_CUDA;
-  }
+      cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) != cudaSuccess)
+    return fail(LSG_ERR_CUDA);
   ctx->pinned_cap = 8192;
-  if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) {
-    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
-    delete ctx;
-    return LSG_ERR_NOMEM;
-  }
+  if (cudaMallocHost(&ctx->pinned, ctx->pinned_cap) != cudaSuccess) return fail(LSG_ERR_NOMEM);
   lsg_model m;
   lsg_default_model(&m);
   build_dev_model(&m, &ctx->model);

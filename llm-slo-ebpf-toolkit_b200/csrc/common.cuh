@@ -272,8 +272,9 @@ struct SortedEvents {
 // sorted_out NULL: records into the context workspace.  `exact`: stable, nanosecond keys, always the radix path.
 int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
                     bool exact, lsg_event *sorted_out, SortedEvents *out);
+// `spans` (optional): their idents are range-checked in the same pass, so a bad span fails before any result is written
 int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                            int64_t window_ns, bool exact, SortedEvents *out);
+                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans);
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                            lsg_event *sorted_out, SortedEvents *out, bool allow_counting);
 int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, uint32_t sig,

@@ -46,6 +46,15 @@ __global__ void k_ident_stats(const lsg_ident *__restrict__ idents, uint32_t n, 
   if ((threadIdx.x & 31) == 0 && m) atomicMax(&st->max_grp, m);
 }
 
+// a span whose ident is outside the table is a caller error, reported from the same readback as the events' (bit 1)
+__global__ void __launch_bounds__(256)
+k_span_check(const lsg_span *__restrict__ spans, size_t n, uint32_t n_idents, EventStats *st) {
+  bool bad = false;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    bad |= load_span(spans + i).ident >= n_idents;
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&st->bad, 2u);
+}
+
 __device__ __forceinline__ bool event_live(const EventRec &e, const lsg_ident *idents, uint32_t n_idents, uint32_t *grp,
                                            bool *bad) {
   *grp = 0;
@@ -607,13 +616,13 @@ int bits_of(uint64_t v) {
 // Sort events by (grp, quantised time).  Fills `out`; records land in `sorted_out` (or a workspace buffer if NULL).
 int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                     int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
-  LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out));
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out, nullptr, 0));
   return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out, !exact);
 }
 
 // phase 1: one pass over the events for the key layout (time range, group count) and the analytic counters
 int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                            int64_t window_ns, bool exact, SortedEvents *out) {
+                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans) {
   memset(out, 0, sizeof *out);
   out->n = n;
   if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_events %zu does not fit 32-bit indices", n);
@@ -633,6 +642,10 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
     k_ident_stats<<<grid_for(ctx, n_idents, 256, 1), 256, 0, ctx->stream>>>(idents, (uint32_t)n_idents, st_dev);
     LSG_LAUNCH_CHECK(ctx);
   }
+  if (spans && n_spans) {
+    k_span_check<<<grid_for(ctx, n_spans, 256, 8), 256, 0, ctx->stream>>>(spans, n_spans, (uint32_t)n_idents, st_dev);
+    LSG_LAUNCH_CHECK(ctx);
+  }
   if (n) {
     k_event_stats<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, st_dev);
     LSG_LAUNCH_CHECK(ctx);
@@ -641,7 +654,8 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
   LSG_CUDA(ctx, cudaMemcpyAsync(pin, st_dev, sizeof init, cudaMemcpyDeviceToHost, ctx->stream));
   LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   EventStats st = *pin;
-  if (st.bad) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if (st.bad & 1u) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if (st.bad & 2u) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
   out->n_live = st.n_live;
   out->n_unsupported = st.n_unsupported;
   KeySpec ks;

@@ -398,3 +398,18 @@ def test_host_pipeline_blocking_and_double_buffered(ctx):
     import llm_slo_ebpf_toolkit_b200 as pkg
     with pytest.raises(pkg.LsgError):
         ctx.call_dev("lsg_pipeline_wait", 0, None)        # nothing in flight
+    # a span whose ident is outside the identity table fails the whole call (LSG_ERR_RANGE), in the pipeline too
+    w_bad = dict(batches[0][1])
+    w_bad["spans"] = w_bad["spans"].copy()
+    w_bad["spans"]["ident"][17] = 1 << 30
+    args, keep, outs = host_args(w_bad)
+    with pytest.raises(pkg.LsgError) as e:
+        ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(A.Counters()))
+    assert e.value.code == -4
+    with pytest.raises(pkg.LsgError) as e:
+        ctx.process_batch(w_bad["spans"], w_bad["events"], w_bad["idents"])
+    assert e.value.code == -4
+    args, keep, outs = host_args(batches[1][1])           # and the context is usable afterwards
+    c = A.Counters()
+    ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(c))
+    check(c, outs, batches[1])
