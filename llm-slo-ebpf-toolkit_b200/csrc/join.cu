@@ -44,6 +44,7 @@ struct JoinParams {
   EventColumns ev;
   const uint32_t *ev_perm;   // sorted position -> input index
   const uint4 *ranges;       // per span in key order: outer [x, y) and inner [z, w) in sorted positions
+  const uint4 *ranges2;      // whole-quanta core [x, y) of the inner window and the +-250 ms part [z, w) of the inner range
   const lsg_ident *idents;
   const uint2 *ident_pc;     // per identity row: (pod, service+node class)
   uint32_t n_idents;
@@ -78,12 +79,14 @@ __global__ void __launch_bounds__(256)
 k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ span_perm, size_t n_spans,
               const KeyT *__restrict__ keys, const uint32_t *__restrict__ bins, uint32_t n_live, KeySpec ks,
               const lsg_ident *__restrict__ idents,
-              uint32_t n_idents, int64_t W, uint4 *__restrict__ ranges, unsigned long long *__restrict__ counters) {
+              uint32_t n_idents, int64_t W, uint4 *__restrict__ ranges, uint4 *__restrict__ ranges2,
+              unsigned long long *__restrict__ counters) {
   const uint64_t ts_max_q = ((uint64_t)1 << ks.tbits) - 1;
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_spans; q += (size_t)gridDim.x * blockDim.x) {
     const size_t si = span_perm ? span_perm[q] : q;
     const SpanRec s = load_span(spans + si);
     uint4 r = make_uint4(n_live, n_live, n_live, n_live);
+    uint4 r2 = r;   // x, y: the events of the quanta that lie wholly inside the exact inner window; z, w: superset of +-250 ms
     if (s.ident >= n_idents) {
       atomicOr((unsigned int *)&counters[5], 1u);
     } else {
@@ -120,10 +123,37 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
         search(Wi, r.x, r.y, &r.z, &r.w);                           // inside the outer range: a short search
         // a span whose own time lies outside the events' time range was clamped into the key space: its inner
         // range is still a superset, but the tile kernel's 32-bit time deltas are not safe for it -> k_join_big
-        if (tc != s.ts) r.z = r.w = 0xffffffffu;
+        if (tc != s.ts) {
+          r.z = r.w = 0xffffffffu;
+        } else {
+          // positions of whole quanta, from the span's exact time this time (these need not be monotone): events of the
+          // quanta in [qa, qb] are inside |dt| <= Wi without looking at them; tiers 2-3 need |dt| <= 250 ms (dns.go:61-68)
+          auto pos_of_quantum = [&](uint64_t qv) -> uint32_t {   // first event of the group at or after quantum qv
+            if (qv > ts_max_q) return r.w;
+            const KeyT k = (KeyT)(((uint64_t)grp << ks.tbits) | qv);
+            if (bins) return bins[(uint32_t)k];
+            return r.z + lower_bound_keys<KeyT>(keys + r.z, r.w - r.z, k);
+          };
+          const uint64_t quantum = (uint64_t)1 << ks.shift;
+          const uint64_t off = (uint64_t)s.ts - (uint64_t)ks.ts_min;
+          const uint64_t qa = off > (uint64_t)Wi ? (off - (uint64_t)Wi + quantum - 1) >> ks.shift : 0;   // first quantum starting at or after ts - Wi
+          const uint64_t qb1 = (off + (uint64_t)Wi + 1) >> ks.shift;                                         // first quantum NOT ending at or before ts + Wi
+          if (qa < qb1) {
+            r2.x = max(r.z, min(r.w, pos_of_quantum(qa)));
+            r2.y = max(r2.x, min(r.w, pos_of_quantum(qb1)));
+          } else {
+            r2.x = r2.y = r.w;
+          }
+          const uint64_t W2 = (uint64_t)(Wi < 250 * kMs ? Wi : 250 * kMs);
+          const uint64_t qc = off > W2 ? (off - W2) >> ks.shift : 0;
+          const uint64_t qd1 = ((off + W2) >> ks.shift) + 1;
+          r2.z = max(r.z, min(r.w, pos_of_quantum(qc)));
+          r2.w = max(r2.z, min(r.w, pos_of_quantum(qd1)));
+        }
       }
     }
     ranges[q] = r;
+    ranges2[q] = r2;
   }
 }
 
@@ -395,10 +425,13 @@ struct TileSmem {
   uint32_t trsig[TM_CAP];
   uint4 span[JT_CH][2];
   uint4 rng[JT_CH];
+  uint4 rng2[JT_CH];
   uint32_t sidx[JT_CH];
   uint16_t note[TM_LIST][JT_CH];    // entry-major: consecutive spans, consecutive halfwords
   uint32_t n_note[JT_CH];           // candidates noted per span (may exceed TM_LIST: then the span is redone by k_join_big)
   uint32_t n_tr[JT_CH];             // trace-id matches per span (tier 1), candidates or not
+  uint32_t n_tr_in[JT_CH];          // those of them inside the inner window
+  uint32_t cls_min, cls_max;        // over the tile's events: equal when the tile holds one (service, node) class
   uint32_t hkey[TM_HASH];           // trace id, 0 = empty
   uint16_t hhead[TM_HASH];          // first span of the chain for that trace id
   uint16_t hnext[JT_CH];            // next span with the same trace id
@@ -432,6 +465,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     // ---- stage the chunk's spans: input index, ranges, record (two 16-byte halves per span); clear the hash
     if ((int)tid < nq) {
       sm.rng[tid] = p.ranges[q0 + tid];
+      sm.rng2[tid] = p.ranges2[q0 + tid];
       sm.sidx[tid] = p.span_perm ? p.span_perm[q0 + tid] : (uint32_t)(q0 + tid);
     }
     if ((int)tid < nq) {
@@ -465,6 +499,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     int i0 = 0;
     while (i0 < nq) {
       const uint32_t A = sm.rng[i0].x & ~3u;   // 16-byte aligned start for every column
+      if (tid == 0) { sm.cls_min = 0xffffffffu; sm.cls_max = 0u; }   // published by the barrier below
       // spans of the chunk whose outer range still ends inside a tile that starts at A (ranges are monotone)
       const bool fits = (int)tid >= i0 && (int)tid < nq && sm.rng[tid].y - A <= (uint32_t)(TM_CAP - 4);
       const int n_fit = __syncthreads_count(fits);
@@ -487,21 +522,27 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           bulk_g2s(sm.conn, p.ev.conn + A, count * 4u, &sm.bar);
         }
       }
-      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; }
+      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
+      const uint32_t live_beg = sm.rng[i0].x - A, live_end = min(count, sm.rng[i1 - 1].y - A);
       if (count) {
         mbar_wait(&sm.bar, phase);
         phase ^= 1;
-        // identity row -> (pod, class), once per staged event instead of once per (span, event) pair
+        // identity row -> (pod, class), once per staged event instead of once per (span, event) pair; and whether
+        // the events the chunk's spans can reach all carry one class (then tier 4 is counted, not enumerated)
+        uint32_t cmin = 0xffffffffu, cmax = 0u;
         for (uint32_t o = tid; o < count; o += JT_THREADS) {
           const uint32_t row = sm.pod[o];
           const uint2 pc = row < p.n_idents ? __ldg(p.ident_pc + row) : make_uint2(0u, 0u);   // padding past the last event
           sm.pod[o] = pc.x;
           sm.cls[o] = pc.y;
+          if (o >= live_beg && o < live_end) { cmin = min(cmin, pc.y); cmax = max(cmax, pc.y); }
         }
+        cmin = __reduce_min_sync(0xffffffffu, cmin);
+        cmax = __reduce_max_sync(0xffffffffu, cmax);
+        if (lane == 0 && cmin <= cmax) { atomicMin(&sm.cls_min, cmin); atomicMax(&sm.cls_max, cmax); }
       }
       __syncthreads();
       // ---- tier 1: every event of the tile probes the hash once
-      const uint32_t live_end = min(count, sm.rng[i1 - 1].y - A);
       for (uint32_t o = tid; o < live_end; o += JT_THREADS) {
         const uint32_t tr = sm.trsig[o] >> 4;
         if (tr == 0) continue;
@@ -517,6 +558,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           const int64_t s_ts = (int64_t)(((uint64_t)sm.span[k][0].y << 32) | sm.span[k][0].x);
           if (lsg_absdiff(s_ts, e_ts) > W) continue;                  // outer window, dns.go:54-56
           atomicAdd(&sm.n_tr[k], 1u);
+          if (lsg_absdiff(s_ts, e_ts) <= Wi) atomicAdd(&sm.n_tr_in[k], 1u);
           if (cut >= 1) {
             const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
             if (at < TM_LIST) sm.note[at][k] = (uint16_t)((LSG_TIER_TRACE << 12) | o);
@@ -525,6 +567,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       }
       __syncthreads();   // the hash pass (short, evenly spread) is complete: from here on a span only needs its own two lanes
       // ---- tiers 2-4: thread (2k + h) walks half h of span k's inner range
+      const bool uniform = sm.cls_min == sm.cls_max;
       const int k = i0 + (int)(tid >> 1);
       const unsigned h = tid & 1;
       const bool live = k < i1;
@@ -543,39 +586,78 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           const uint32_t s_pod = spc.x, s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
           const bool pid_ok = s.pid != 0, conn_ok = s.conn != 0;
           const uint32_t zo = rg.z - A, wo = rg.w - A;
-          const uint32_t mid = zo + ((wo - zo) >> 1);
-          const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
           const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
           const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);   // little endian: low words at even indices
           const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;       // event trace ids are < 2^28
-          for (uint32_t o = beg; o < end; ++o) {
-            // every operand is loaded up front (five independent shared-memory loads), the decision is predicate arithmetic
-            const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_cls = sm.cls[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
-            bool in, in100, in250;
-            if (T32) {   // |dt| < 2^31 ns for every event of an inner range: 32-bit arithmetic is exact
+          // |event time - span time|; when T32, |dt| < 2^31 ns for every event of an inner range and 32 bits are exact
+          auto absdt = [&](uint32_t o) -> uint64_t {
+            if (T32) {
               const int32_t d = (int32_t)(ts_lo[2 * o] - s_lo);
-              const uint32_t ad = (uint32_t)(d < 0 ? -d : d);
-              in = ad <= (uint32_t)Wi; in100 = ad <= (uint32_t)(100 * kMs); in250 = ad <= (uint32_t)(250 * kMs);
-            } else {
-              const uint64_t ad = lsg_absdiff(s.ts, sm.ts[o]);
-              in = ad <= Wi; in100 = ad <= (uint64_t)(100 * kMs); in250 = ad <= (uint64_t)(250 * kMs);
+              return (uint64_t)(uint32_t)(d < 0 ? -d : d);
             }
-            const bool same_pod = pod_ok & (e_pod == s_pod), same_sn = e_cls == s_cls;
-            const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
-            const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
-            const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
-            // inside min(W, 500 ms), not a trace-id match (those belong to the hash pass), and some tier applies
-            const bool m = in & ((e_trsig >> 4) != no_trace) & (tier != 0);
-            n_match += m;
-            const bool low = m & (tier > cut);                                   // correlator.go:83-86
-            n_low += low;
-            if (m & !low) {
-              if (full) {
-                n_unlisted++;
-              } else {
-                const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-                if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
-              }
+            return lsg_absdiff(s.ts, sm.ts[o]);
+          };
+          auto note = [&](int tier, uint32_t o) {
+            if (full) {
+              n_unlisted++;
+            } else {
+              const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+              if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
+            }
+          };
+          if (cut < 4 && uniform) {
+            // Every event this chunk can reach carries the same (service, node) class, and a service+node match is
+            // below the threshold: it is only counted (correlator.go:83-86).  So count instead of enumerating:
+            //   tier 4 = events inside the inner window - trace-id matches among them - tier 2/3 matches,
+            // where the window count is the whole quanta [x1, y1) plus an exact test on the two ragged edges, the
+            // trace-id matches come from the hash pass, and tiers 2-3 are enumerated on the +-250 ms part only.
+            const uint4 r2 = sm.rng2[k];
+            const uint32_t x1 = r2.x - A, y1 = r2.y - A, z2 = r2.z - A, w2 = r2.w - A;
+            uint32_t n_in = h ? 0u : y1 - x1;
+            const uint32_t eb = h ? y1 : zo, ee = h ? wo : x1;      // lane 0: left edge, lane 1: right edge
+            for (uint32_t o = eb; o < ee; ++o) n_in += absdt(o) <= Wi;
+            const uint32_t m2 = z2 + ((w2 - z2) >> 1);
+            const uint32_t fb = h ? m2 : z2, fe = h ? w2 : m2;
+            uint32_t n23 = 0;
+            for (uint32_t o = fb; o < fe; ++o) {
+              const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
+              const uint64_t ad = absdt(o);
+              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
+              const bool same_pod = pod_ok & (e_pod == s_pod);
+              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
+              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
+              const int tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
+              const bool m = in & ((e_trsig >> 4) != no_trace) & (t2 | t3);
+              n23 += m;
+              n_match += m;
+              const bool low = m & (tier > cut);                                   // correlator.go:83-86
+              n_low += low;
+              if (m & !low) note(tier, o);
+            }
+            if (s_cls == sm.cls_min) {   // the span belongs to the tile's class: what is left inside the window is tier 4
+              uint32_t n4 = n_in - n23;                                            // may wrap per lane; the two-lane sum does not
+              if (!h) n4 -= sm.n_tr_in[k];
+              n_match += n4;
+              n_low += n4;
+            }
+          } else {
+            const uint32_t mid = zo + ((wo - zo) >> 1);
+            const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
+            for (uint32_t o = beg; o < end; ++o) {
+              // every operand is loaded up front (independent shared-memory loads), the decision is predicate arithmetic
+              const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_cls = sm.cls[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
+              const uint64_t ad = absdt(o);
+              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
+              const bool same_pod = pod_ok & (e_pod == s_pod), same_sn = e_cls == s_cls;
+              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
+              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
+              const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
+              // inside min(W, 500 ms), not a trace-id match (those belong to the hash pass), and some tier applies
+              const bool m = in & ((e_trsig >> 4) != no_trace) & (tier != 0);
+              n_match += m;
+              const bool low = m & (tier > cut);                                   // correlator.go:83-86
+              n_low += low;
+              if (m & !low) note(tier, o);
             }
           }
         }
@@ -797,7 +879,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   LSG_CUDA(ctx, cudaMemsetAsync(a.counters, 0, 8 * sizeof(uint64_t), ctx->stream));
   if (a.n_spans == 0) return 0;
   void *rv = nullptr;
-  LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * (sizeof(uint4) + sizeof(uint32_t)), &rv));
+  LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * (2 * sizeof(uint4) + sizeof(uint32_t)), &rv));
+  uint4 *ranges2 = (uint4 *)rv + a.n_spans;
   const uint32_t n_live = (uint32_t)a.ev.n_live;
   {
     ProfScope ps(ctx, PK_RANGES);
@@ -806,16 +889,16 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
     if (a.ev.key.bits <= 31)
       k_span_ranges<uint32_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint32_t *)a.ev.keys,
                                                                       a.ev.bins, n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
-                                                                      a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
+                                                                      a.window_ns, (uint4 *)rv, ranges2, (unsigned long long *)a.counters);
     else
       k_span_ranges<uint64_t><<<(unsigned)blocks, 256, 0, ctx->stream>>>(a.spans, a.span_perm, a.n_spans, (const uint64_t *)a.ev.keys,
                                                                       a.ev.bins, n_live, a.ev.key, a.idents, (uint32_t)a.n_idents,
-                                                                      a.window_ns, (uint4 *)rv, (unsigned long long *)a.counters);
+                                                                      a.window_ns, (uint4 *)rv, ranges2, (unsigned long long *)a.counters);
     LSG_LAUNCH_CHECK(ctx);
   }
   JoinParams p;
   p.spans = a.spans; p.span_perm = a.span_perm; p.n_spans = a.n_spans;
-  p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv;
+  p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv; p.ranges2 = ranges2;
   p.idents = a.idents; p.n_idents = (uint32_t)a.n_idents;
   p.ident_pc = a.ident_pc;
   if (!p.ident_pc) LSG_TRY(lsg_ident_classes(ctx, a.idents, a.n_idents, &p.ident_pc));
@@ -827,7 +910,7 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   const size_t n_chunks = (a.n_spans + JT_CH - 1) / JT_CH;
   const size_t smem = sizeof(TileSmem);
   // spans that do not fit a tile are listed for k_join_big; the list lives behind the ranges
-  uint32_t *big_list = (uint32_t *)((char *)rv + a.n_spans * sizeof(uint4));
+  uint32_t *big_list = (uint32_t *)((char *)rv + a.n_spans * 2 * sizeof(uint4));
   unsigned int *big_count = (unsigned int *)(a.counters + 6);
   ProfScope ps(ctx, PK_JOIN);
   // persistent grid: exactly as many CTAs as are resident at once (SM count x occupancy), each striding over chunks

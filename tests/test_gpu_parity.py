@@ -50,6 +50,10 @@ def test_random_string_batches_vs_string_oracle(ctx, seed):
     (2000, 0.7, 3, 36, 64, 2), (2000, 0.7, 3, 3600, 64, 2), (100, 0.85, 1, 36, 16, 1), (5000, 0.6, 8, 20, 8, 4),
     (2000, 1.0, 2, 36, 64, 2), (250, 0.7, 5, 4, 4, 2), (2000, 0.6, 12, 36, 16, 2), (1000, 0.7, 32, 10, 8, 2),
     (2000, 0.7, 3, 3600, 4096, 2),   # 2048 groups x 2^17 quanta: too many keys for the counting sort -> radix path
+    # the counted (not enumerated) service+node tier: inner window below / between / above the tier limits, a time
+    # quantum wider than the inner window, one-pod and four-pod classes, every cut below tier 4
+    (50, 0.7, 3, 20, 16, 2), (400, 0.7, 3, 20, 16, 2), (20000, 0.7, 3, 60, 16, 2), (700, 0.95, 3, 20, 16, 1),
+    (2000, 0.85, 4, 30, 16, 4), (499, 0.66, 2, 10, 8, 2), (501, 0.8, 3, 10, 8, 2),
 ])
 def test_synthetic_vs_indexed_oracle(ctx, window_ms, thr, fanout, horizon_s, n_pods, ppg):
     cfg = synth.config(200_000, 20_000, n_pods, max(ppg, 8 if n_pods >= 8 else n_pods), ppg, seed=window_ms + fanout,
@@ -59,6 +63,26 @@ def test_synthetic_vs_indexed_oracle(ctx, window_ms, thr, fanout, horizon_s, n_p
     want = O.process_batch(w["spans"], w["events"], w["idents"], window_ms * 1_000_000, thr, fanout, indexed=True, nthreads=8)
     _eq_batch(got, want)
     assert (got["cand_event"] != A.NONE).sum() > 1000
+
+
+def test_counted_tier4_with_empty_service_or_node(ctx):
+    """Tiles whose events all carry one (service, node) class count the service+node tier instead of enumerating it;
+    rows with an empty service or node have no class and must never match on that tier (dns.go:69-73)."""
+    cfg = synth.config(120_000, 12_000, 16, 8, 2, seed=77, horizon_ns=30_000_000_000)
+    w = synth.generate_host(cfg)
+    for variant in range(4):
+        ids = w["idents"].copy()
+        if variant == 0:
+            ids["service"][:] = 0                      # no row has a class: every tile is uniform with class 0
+        elif variant == 1:
+            ids["node"][ids["grp"] == ids["grp"].max()] = 0   # one group without a class, the others keep theirs
+        elif variant == 2:
+            ids["service"][::2] = 0                    # every group holds one row with and one without a class: mixed tiles
+        else:
+            ids["pod"][:] = 0                          # no pod anywhere: only trace ids and service+node can match
+        got = ctx.process_batch(w["spans"], w["events"], ids)
+        want = O.process_batch(w["spans"], w["events"], ids, indexed=True, nthreads=8)
+        _eq_batch(got, want)
 
 
 def test_brute_force_subsample(ctx):
