@@ -384,8 +384,8 @@ def main():
         "radix_hist": (32 + 8) * n if counting else key_bytes * n,                  # count keys: the records once, (key, rank) out
         "radix_scatter": (8 + 4) * n if counting else 2 * (key_bytes + 4) * n,      # place: (key, rank) in, index out
         "gather_events": (4 + 32 + 32) * n,
-        "join": 32 * n + 4 * n + 32 * s_ + 16 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # records + index once, span, ranges, outputs
-        "span_ranges": 32 * s_ + 16 * s_,
+        "join": 32 * n + 4 * n + 32 * s_ + 32 * s_ + s_ * (f * 5 + A.NSIG * 8 + 8),   # records + index once, span, ranges, outputs
+        "span_ranges": 32 * s_ + 32 * s_,
         "incident_features": A.NSIG * 8 * s_ + 4 * s_ + 2 * A.NSIG * 8 * i_, "attribute": (A.NSIG * 8 + A.NDOM * 8 + 1) * i_,
         "confusion": (A.NDOM * 8 + 7) * i_,
     }
