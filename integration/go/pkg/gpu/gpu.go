@@ -1,0 +1,261 @@
+//go:build gpu
+
+// Package gpu binds include/llmslo_gpu.h.  It knows nothing about the reference's own types (pkg/correlation,
+// pkg/attribution import it, not the other way round).
+package gpu
+
+/*
+#cgo LDFLAGS: -lllmslo_gpu
+#include <stdlib.h>
+#include "llmslo_gpu.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"runtime"
+	"sync"
+	"unsafe"
+)
+
+// Memory layout mirrors of the C records (checked against lsg_abi_sizes in New).
+type Event struct {
+	TsNs     int64
+	Value    float64
+	Ident    uint32
+	PID      uint32
+	Conn     uint32
+	TraceSig uint32 // trace id << 4 | signal index
+}
+
+type Span struct {
+	TsNs     int64
+	Ident    uint32
+	PID      uint32
+	Conn     uint32
+	Trace    uint32
+	Incident uint32
+	Reserved uint32
+}
+
+type Ident struct{ Pod, Node, Service, Grp uint32 }
+
+type Debug struct{ Unmatched, LowConfidence, FanoutDropped, UnsupportedType uint64 }
+
+type Eval struct {
+	TP, FP, FN, TN              uint64
+	TierCorrect, TierComparable uint64
+	PredictedByTier             [5]uint64 // predicted pairs per tier code
+	MatchedByTier               [5]uint64 // all pairs per Match() tier code, [0] = unmatched
+}
+
+const (
+	NSig           = int(C.LSG_NSIG)
+	NDom           = int(C.LSG_NDOM)
+	SigUnsupported = uint32(C.LSG_SIG_UNSUPPORTED)
+	None           = uint32(0xffffffff)
+	TraceBits      = 28
+	MaxActual      = int(C.LSG_MAX_ACTUAL)
+)
+
+// TsZero marks time.Time{} (IsZero), which never matches (dns.go:107-113).
+var TsZero = int64(C.LSG_TS_ZERO)
+
+// Signals in DefaultLikelihoods order (bayesian.go:69-189); the index is the signal's slot everywhere in the ABI.
+var Signals = [...]string{"dns_latency_ms", "tcp_retransmits_total", "runqueue_delay_ms", "connect_latency_ms",
+	"tls_handshake_ms", "cpu_steal_pct", "cfs_throttled_ms", "mem_reclaim_latency_ms", "disk_io_latency_ms",
+	"syscall_latency_ms", "connect_errors_total", "tls_handshake_fail_total"}
+
+// Domains in AllDomains order (bayesian.go:23-34).
+var Domains = [...]string{"network_dns", "network_egress", "cpu_throttle", "memory_pressure", "provider_throttle",
+	"provider_error", "retrieval_backend", "unknown"}
+
+// Tier names by tier code (dns.go:58-73); code 0 = no match.
+var Tiers = [...]string{"", "trace_id_exact", "pod_pid_100ms", "pod_conn_250ms", "service_node_500ms"}
+
+// TierConfidence by tier code (dns.go:58-73).
+var TierConfidence = [...]float64{0, 1.0, 0.9, 0.8, 0.65}
+
+// Ctx wraps lsg_ctx.  A context is single-threaded: calls run under the mutex on a locked OS thread so the CUDA
+// primary context stays on one thread.  cgo calls block the goroutine, which is fine for batch work.
+type Ctx struct {
+	mu sync.Mutex
+	h  *C.lsg_ctx
+}
+
+var (
+	defaultOnce sync.Once
+	defaultCtx  *Ctx
+	defaultErr  error
+)
+
+// Default returns the process-wide context on device 0 (what the *_gpu.go files use).
+func Default() (*Ctx, error) {
+	defaultOnce.Do(func() { defaultCtx, defaultErr = New(0) })
+	return defaultCtx, defaultErr
+}
+
+// MustDefault panics when there is no usable GPU: the gpu build has no CPU fallback.
+func MustDefault() *Ctx {
+	c, err := Default()
+	if err != nil {
+		panic(err)
+	}
+	return c
+}
+
+func New(device int) (*Ctx, error) {
+	var sizes [11]C.size_t
+	C.lsg_abi_sizes(&sizes[0], C.int(len(sizes)))
+	if uintptr(sizes[0]) != unsafe.Sizeof(Event{}) || uintptr(sizes[1]) != unsafe.Sizeof(Span{}) ||
+		uintptr(sizes[2]) != unsafe.Sizeof(Ident{}) || uintptr(sizes[3]) != unsafe.Sizeof(Debug{}) ||
+		uintptr(sizes[4]) != unsafe.Sizeof(Eval{}) {
+		return nil, fmt.Errorf("llmslo_gpu: struct layout differs from the library's (%s)", C.GoString(C.lsg_version()))
+	}
+	var h *C.lsg_ctx
+	if rc := C.lsg_create(C.int(device), nil, &h); rc != 0 {
+		return nil, fmt.Errorf("llmslo_gpu: lsg_create failed with code %d (no CPU fallback)", int(rc))
+	}
+	return &Ctx{h: h}, nil
+}
+
+func (c *Ctx) Close() {
+	c.mu.Lock()
+	defer c.mu.Unlock()
+	if c.h != nil {
+		C.lsg_destroy(c.h)
+		c.h = nil
+	}
+}
+
+func (c *Ctx) err(rc C.int) error {
+	if rc == 0 {
+		return nil
+	}
+	return fmt.Errorf("llmslo_gpu: %s (code %d)", C.GoString(C.lsg_last_error(c.h)), int(rc))
+}
+
+func (c *Ctx) enter() func() {
+	c.mu.Lock()
+	runtime.LockOSThread()
+	return func() { runtime.UnlockOSThread(); c.mu.Unlock() }
+}
+
+func ptr[T any](s []T) unsafe.Pointer {
+	if len(s) == 0 {
+		return nil
+	}
+	return unsafe.Pointer(unsafe.SliceData(s))
+}
+
+// MatchPairs is Match (dns.go:50-76) over pre-paired records plus the counters of EvaluateLabeledPairs
+// (evaluator.go:90-167).  expectedTier: 0 = no expectation.
+func (c *Ctx) MatchPairs(spans []Span, events []Event, idents []Ident, windowNS int64, threshold float64,
+	expectedMatch, expectedTier []uint8) (tier, predicted []uint8, ev Eval, err error) {
+	defer c.enter()()
+	n := len(spans)
+	tier, predicted = make([]uint8, n), make([]uint8, n)
+	rc := C.lsg_match_pairs(c.h, (*C.lsg_span)(ptr(spans)), (*C.lsg_event)(ptr(events)), C.size_t(n),
+		(*C.lsg_ident)(ptr(idents)), C.size_t(len(idents)), C.int64_t(windowNS), C.double(threshold),
+		(*C.uint8_t)(ptr(expectedMatch)), (*C.uint8_t)(ptr(expectedTier)), (*C.uint8_t)(ptr(tier)),
+		(*C.uint8_t)(ptr(predicted)), (*C.lsg_eval)(unsafe.Pointer(&ev)))
+	return tier, predicted, ev, c.err(rc)
+}
+
+// BatchResult is what ProcessBatch needs to rebuild the attribute maps (processor.go:29-49).
+type BatchResult struct {
+	Fanout    int
+	CandEvent []uint32  // n_spans * Fanout, None = empty slot; kept candidates in the reference's order
+	CandTier  []uint8   // n_spans * Fanout
+	Attr      []float64 // n_spans * NSig, NaN = absent; max(base, kept values) per signal (correlator.go:106-112)
+	Conf      []float64 // llm.ebpf.correlation_confidence, 0 = not set (correlator.go:113-118)
+	Retrieval []float64 // DecomposeRetrieval total (correlator.go:179-194), set when > 0
+	Debug     Debug
+}
+
+// ProcessBatch is the body of Correlator.ProcessBatch.  attrBase (optional) holds the spans' existing values of
+// the twelve eBPF attributes, NaN = absent.
+func (c *Ctx) ProcessBatch(spans []Span, events []Event, idents []Ident, windowNS int64, threshold float64,
+	fanout int, attrBase []float64) (BatchResult, error) {
+	defer c.enter()()
+	if fanout <= 0 {
+		fanout = 3 // correlator.go:62-66
+	}
+	n := len(spans)
+	r := BatchResult{Fanout: fanout, CandEvent: make([]uint32, n*fanout), CandTier: make([]uint8, n*fanout),
+		Attr: make([]float64, n*NSig), Conf: make([]float64, n), Retrieval: make([]float64, n)}
+	rc := C.lsg_process_batch(c.h, (*C.lsg_span)(ptr(spans)), C.size_t(n), (*C.lsg_event)(ptr(events)),
+		C.size_t(len(events)), (*C.lsg_ident)(ptr(idents)), C.size_t(len(idents)), C.int64_t(windowNS),
+		C.double(threshold), C.int(fanout), (*C.double)(ptr(attrBase)), (*C.uint32_t)(ptr(r.CandEvent)),
+		(*C.uint8_t)(ptr(r.CandTier)), (*C.double)(ptr(r.Attr)), (*C.double)(ptr(r.Conf)),
+		(*C.double)(ptr(r.Retrieval)), nil, (*C.lsg_debug)(unsafe.Pointer(&r.Debug)))
+	return r, c.err(rc)
+}
+
+// Model is lsg_model: the flattened BayesianAttributor (bayesian.go:36-44).  Lik is NaN where a domain is missing
+// from a signal's table (likelihoodFor then uses 0.5, bayesian.go:293-296).
+type Model struct {
+	Prior    [8]float64
+	Lik      [12][8]float64
+	Thresh   [12]float64
+	LogExtra [8]float64
+	SigMask  uint32
+	Reserved uint32
+}
+
+func DefaultModel() Model {
+	var m Model
+	C.lsg_default_model((*C.lsg_model)(unsafe.Pointer(&m)))
+	return m
+}
+
+func (c *Ctx) SetModel(m *Model) error {
+	defer c.enter()()
+	return c.err(C.lsg_set_model(c.h, (*C.lsg_model)(unsafe.Pointer(m))))
+}
+
+// Attribute is BayesianAttributor.Attribute for a batch: signals is n*NSig (NaN = absent), hasSignals marks
+// samples with len(Signals) > 0 (the others keep ruleLabel, bayesian.go:318-320).  posterior is n*NDom in
+// AllDomains order; top1 the first maximum (sort.SliceStable, bayesian.go:279-281); elevMask bit s = signal s
+// elevated (bayesian.go:220-226).
+func (c *Ctx) Attribute(signals []float64, hasSignals, ruleLabel []uint8) (posterior []float64, top1 []uint8,
+	elevMask []uint16, err error) {
+	defer c.enter()()
+	n := len(signals) / NSig
+	posterior, top1, elevMask = make([]float64, n*NDom), make([]uint8, n), make([]uint16, n)
+	rc := C.lsg_attribute(c.h, (*C.double)(ptr(signals)), (*C.uint8_t)(ptr(hasSignals)), (*C.uint8_t)(ptr(ruleLabel)),
+		C.size_t(n), (*C.double)(ptr(posterior)), (*C.uint8_t)(ptr(top1)), (*C.uint16_t)(ptr(elevMask)))
+	return posterior, top1, elevMask, c.err(rc)
+}
+
+// Confusion is lsg_confusion_out.
+type Confusion struct {
+	Matrix   [16][8]uint64
+	N        uint64
+	Correct  uint64
+	Partial  uint64
+	Coverage [9][9]uint64 // [found][len(expected)]
+}
+
+// ConfusionCounts is BuildConfusionMatrix + the integer numerators of Accuracy / PartialAccuracy /
+// CoverageAccuracy (pipeline.go:65-185).  actual: 0..7 = AllDomains, 8..15 = other strings (numbered by the caller);
+// expected: up to eight 4-bit domain indices per incident, first in the low nibble, 0xF = not one of AllDomains;
+// expectedN: how many; posterior: n*NDom, NaN where the prediction carries no hypothesis for the domain.
+func (c *Ctx) ConfusionCounts(actual, predicted []uint8, expected []uint32, expectedN []uint8, posterior []float64,
+	coverageThr, hypFloor float64) (Confusion, error) {
+	defer c.enter()()
+	var out Confusion
+	rc := C.lsg_confusion(c.h, (*C.uint8_t)(ptr(actual)), (*C.uint8_t)(ptr(predicted)), (*C.uint32_t)(ptr(expected)),
+		(*C.uint8_t)(ptr(expectedN)), (*C.double)(ptr(posterior)), C.double(coverageThr), C.double(hypFloor),
+		C.size_t(len(actual)), (*C.lsg_confusion_out)(unsafe.Pointer(&out)))
+	return out, c.err(rc)
+}
+
+// SegmentQuantiles is quantile() (pkg/slo/calculator.go:121-149) for many value lists in one call.
+func (c *Ctx) SegmentQuantiles(values []float64, segment []uint32, nSegments int, q []float64) ([]float64, []uint64, error) {
+	defer c.enter()()
+	out, cnt := make([]float64, nSegments*len(q)), make([]uint64, nSegments)
+	rc := C.lsg_segment_quantiles(c.h, (*C.double)(ptr(values)), (*C.uint32_t)(ptr(segment)), C.size_t(len(values)),
+		C.size_t(nSegments), (*C.double)(ptr(q)), C.size_t(len(q)), (*C.double)(ptr(out)), (*C.uint64_t)(ptr(cnt)))
+	return out, cnt, c.err(rc)
+}
