@@ -270,6 +270,9 @@ typedef struct {
   lsg_debug debug;
   lsg_confusion_out confusion;
   uint64_t events, spans, incidents, candidates, kept;
+  uint64_t bad_idents; /* non-zero: some event's or span's ident was outside the identity table and the batch's results
+                          are void.  lsg_pipeline and lsg_pipeline_wait turn it into LSG_ERR_RANGE; a caller of
+                          lsg_pipeline_dev checks it after reading the counters back (summed over ranks it stays non-zero) */
 } lsg_counters;
 #define LSG_COUNTER_WORDS (sizeof(lsg_counters) / 8)
 

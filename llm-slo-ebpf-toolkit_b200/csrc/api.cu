@@ -148,19 +148,21 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   return 0;
 }
 
-void fill_debug(lsg_debug *d, const uint64_t *jc, const SortedEvents &sorted, size_t n_spans) {
-  const uint64_t n_supported = (uint64_t)sorted.n - sorted.n_unsupported;
-  d->unsupported_type = sorted.n_unsupported * (uint64_t)n_spans;   // correlator.go:73-77, once per span
+void fill_debug(lsg_debug *d, const uint64_t *jc, const SortedEvents &sorted, uint64_t n_unsupported, size_t n_spans) {
+  const uint64_t n_supported = (uint64_t)sorted.n - n_unsupported;
+  d->unsupported_type = n_unsupported * (uint64_t)n_spans;   // correlator.go:73-77, once per span
   d->unmatched = n_supported * (uint64_t)n_spans - jc[0];           // every supported pair that did not match
   d->low_confidence = jc[1];
   d->fanout_dropped = jc[2];
 }
 
 __global__ void k_finalize_counters(const unsigned long long *__restrict__ jc, unsigned long long n_events,
-                                    unsigned long long n_unsupported, unsigned long long n_spans,
+                                    const LsgBatchStats *__restrict__ stats, unsigned long long n_spans,
                                     unsigned long long n_incidents, unsigned long long *__restrict__ out) {
-  // layout = lsg_counters: debug[4] | confusion | events spans incidents candidates kept
+  // layout = lsg_counters: debug[4] | confusion | events spans incidents candidates kept bad_idents
   const int tail = 4 + (int)(sizeof(lsg_confusion_out) / 8);
+  const unsigned long long n_unsupported = stats->n_unsupported;
+  out[tail + 5] = (stats->bad != 0 || jc[5] != 0) ? 1ull : 0ull;
   out[0] = (n_events - n_unsupported) * n_spans - jc[0];
   out[1] = jc[1];
   out[2] = jc[2];
@@ -413,11 +415,15 @@ int lsg_process_batch_dev(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, c
   SortedEvents sorted;
   LSG_TRY(process_batch_core(ctx, spans, n_spans, events, n_events, idents, n_idents, window_ns, threshold, fanout, attr_base,
                              cand_event, cand_tier, attr_out, conf_out, retrieval_out, n_cand_out, &jc_dev, &sorted));
-  uint64_t *pin = (uint64_t *)ctx->pinned;
-  LSG_CUDA(ctx, cudaMemcpyAsync(pin, jc_dev, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  // one readback: the batch statistics (start of WS_SMALL) and the join's counters behind them
+  char *pin = (char *)ctx->pinned;
+  LSG_CUDA(ctx, cudaMemcpyAsync(pin, sorted.stats_dev, SMALL_JOIN + 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
   LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  if (pin[5]) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
-  if (debug_out) fill_debug(debug_out, pin, sorted, n_spans);
+  const LsgBatchStats st = *(const LsgBatchStats *)pin;
+  const uint64_t *jc = (const uint64_t *)(pin + SMALL_JOIN);
+  if (st.bad & 1u) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if ((st.bad & 2u) || jc[5]) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
+  if (debug_out) fill_debug(debug_out, jc, sorted, st.n_unsupported, n_spans);
   return 0;
 }
 
@@ -598,7 +604,7 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
   LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
                                0.01, a->n_incidents, a->counters_dev + 4));
-  k_finalize_counters<<<1, 1, 0, ctx->stream>>>((const unsigned long long *)jc_dev, a->n_events, sorted.n_unsupported, a->n_spans,
+  k_finalize_counters<<<1, 1, 0, ctx->stream>>>((const unsigned long long *)jc_dev, a->n_events, sorted.stats_dev, a->n_spans,
                                                 a->n_incidents, (unsigned long long *)a->counters_dev);
   LSG_LAUNCH_CHECK(ctx);
   return 0;
@@ -639,6 +645,8 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   if (counters_out) memcpy(counters_out, ctx->pinned, sizeof(lsg_counters));
   if (a->counters_dev) memcpy(a->counters_dev, ctx->pinned, sizeof(lsg_counters));
+  if (((const lsg_counters *)ctx->pinned)->bad_idents)
+    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident is outside the identity table (n_idents=%zu)", a->n_idents);
   return 0;
 }
 
@@ -743,6 +751,8 @@ int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out) {
   LSG_CUDA(ctx, cudaEventSynchronize(ctx->ev_down[slot]));
   ctx->slot_busy[slot] = false;
   if (counters_out) memcpy(counters_out, ctx->slot_counters_host[slot], sizeof(lsg_counters));
+  if (((const lsg_counters *)ctx->slot_counters_host[slot])->bad_idents)
+    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident in the batch of slot %d is outside the identity table", slot);
   return 0;
 }
 

@@ -80,7 +80,8 @@ __device__ __forceinline__ double key_f64(unsigned long long k) {
 // Time, unsupported signal type) get the key (max_grp + 1) << tbits and sort behind everything a span
 // ever searches.
 struct KeySpec {
-  int64_t ts_min;
+  int64_t ts_min;   // origin of the time axis; events before it can match nothing
+  int64_t ts_hi;    // events after it can match nothing (last span + window, or the last live event)
   uint32_t shift;   // time quantum = 2^shift ns
   uint32_t tbits;   // bits of the quantised time
   uint32_t bits;    // total key bits (gbits + tbits)
@@ -258,6 +259,14 @@ struct EventColumns {     // events grouped by key as columns (what the join sta
   const double *val;
   const uint32_t *ident, *pid, *conn, *trsig;
 };
+// what one look at every event (and span) of a batch collects, in device memory at the start of WS_SMALL
+struct LsgBatchStats {
+  long long ts_min, ts_max;                 // over the live events, or over the live spans (see lsg_sort_events_prepare)
+  unsigned long long n_live, n_unsupported; // events; n_live only when the events were looked at before the sort
+  unsigned int max_grp, bad;                // bad: bit 0 an event's, bit 1 a span's ident is outside the identity table
+  unsigned int pad[2];
+};
+
 struct SortedEvents {
   EventColumns col;       // set when the records were not asked for (the join's input)
   const lsg_event *rec;   // set when the caller asked for records (lsg_sort_events_dev)
@@ -266,13 +275,18 @@ struct SortedEvents {
   const uint32_t *bins;   // counting path: bins[k] = start of key k's run, bins[k + 1] its end; NULL on the radix path
   KeySpec key;
   size_t n;               // all events
-  size_t n_live;          // events that can match (they come first)
-  uint64_t n_unsupported; // events with an unsupported signal type
+  size_t n_live;          // upper bound of the events that can match (they come first); exact on the radix path only
+                          // when the key range came from the events
+  const LsgBatchStats *stats_dev;   // device copy, complete once the sort kernels ran (n_unsupported, bad)
+  bool tally_in_sort;               // the sort's first pass adds n_unsupported / bad to stats_dev (key range from the spans)
 };
 // sorted_out NULL: records into the context workspace.  `exact`: stable, nanosecond keys, always the radix path.
 int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, int64_t window_ns,
                     bool exact, lsg_event *sorted_out, SortedEvents *out);
-// `spans` (optional): their idents are range-checked in the same pass, so a bad span fails before any result is written
+// With `spans` the key range comes from the spans (first live span - window .. last live span + window: an event
+// outside it can match nothing and is treated like a dead record), so the events are not read before the sort; the
+// unsupported-type count and the events' ident check then come out of the sort's own first pass (stats_dev).
+// Without spans (the sort as its own entry point) one pass over the events sets the range.
 int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                             int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans);
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,

@@ -32,12 +32,7 @@ constexpr int SORT_TILE = SORT_BLOCK * SORT_IPT;  // 8192 keys per CTA
 constexpr int SORT_NW = SORT_BLOCK / 32;
 
 // ---- statistics that fix the key layout ----------------------------------------------------------
-struct EventStats {
-  long long ts_min, ts_max;
-  unsigned long long n_live, n_unsupported;
-  unsigned int max_grp, bad;
-  unsigned int pad[2];
-};
+using EventStats = LsgBatchStats;
 
 __global__ void k_ident_stats(const lsg_ident *__restrict__ idents, uint32_t n, EventStats *st) {
   unsigned int m = 0;
@@ -46,13 +41,28 @@ __global__ void k_ident_stats(const lsg_ident *__restrict__ idents, uint32_t n, 
   if ((threadIdx.x & 31) == 0 && m) atomicMax(&st->max_grp, m);
 }
 
-// a span whose ident is outside the table is a caller error, reported from the same readback as the events' (bit 1)
+// time range of the spans that can match anything; a span whose ident is outside the table is a caller error (bit 1)
 __global__ void __launch_bounds__(256)
-k_span_check(const lsg_span *__restrict__ spans, size_t n, uint32_t n_idents, EventStats *st) {
+k_span_stats(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
+             EventStats *st) {
+  long long tmin = INT64_MAX, tmax = INT64_MIN;
   bool bad = false;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    bad |= load_span(spans + i).ident >= n_idents;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const SpanRec s = load_span(spans + i);
+    if (s.ident >= n_idents) { bad = true; continue; }
+    if (s.ts == LSG_TS_ZERO || load_ident(idents, s.ident).grp == 0) continue;
+    tmin = min(tmin, (long long)s.ts);
+    tmax = max(tmax, (long long)s.ts);
+  }
+  for (int o = 16; o; o >>= 1) {
+    tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+    tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
+  }
   if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&st->bad, 2u);
+  if ((threadIdx.x & 31) == 0 && tmin <= tmax) {
+    atomicMin(&st->ts_min, tmin);
+    atomicMax(&st->ts_max, tmax);
+  }
 }
 
 __device__ __forceinline__ bool event_live(const EventRec &e, const lsg_ident *idents, uint32_t n_idents, uint32_t *grp,
@@ -63,6 +73,30 @@ __device__ __forceinline__ bool event_live(const EventRec &e, const lsg_ident *i
   if (e.ts == LSG_TS_ZERO) return false;               // zero Time never matches (dns.go:108)
   *grp = load_ident(idents, e.ident).grp;
   return *grp != 0;
+}
+
+// the sort's own look at an event: its key (or "dead"), and what the batch statistics need from it
+struct EventTally {
+  unsigned int unsup = 0;
+  bool bad = false;
+  __device__ __forceinline__ void flush(EventStats *st) {
+    if (!st) return;
+    unsup = __reduce_add_sync(0xffffffffu, unsup);
+    const bool any_bad = __any_sync(0xffffffffu, bad);
+    if ((threadIdx.x & 31) == 0) {
+      if (unsup) atomicAdd(&st->n_unsupported, (unsigned long long)unsup);
+      if (any_bad) atomicOr(&st->bad, 1u);
+    }
+  }
+};
+__device__ __forceinline__ bool event_key(const EventRec &e, const lsg_ident *idents, uint32_t n_idents, const KeySpec &ks,
+                                          EventTally &t, uint64_t *key) {
+  if ((e.trace_sig & 15u) >= LSG_NSIG) t.unsup++;
+  uint32_t g;
+  if (!event_live(e, idents, n_idents, &g, &t.bad)) return false;
+  if (e.ts < ks.ts_min || e.ts > ks.ts_hi) return false;   // further than the window from every span
+  *key = lsg_make_key(ks, g, e.ts);
+  return true;
 }
 
 __global__ void __launch_bounds__(256)
@@ -111,16 +145,16 @@ k_event_stats(const lsg_event *__restrict__ events, size_t n, const lsg_ident *_
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 k_event_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
-             KeySpec ks, KeyT *__restrict__ keys) {
+             KeySpec ks, KeyT *__restrict__ keys, EventStats *st) {
+  EventTally tally;
 #pragma unroll 4
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     EventRec e = load_event(events + i);
-    uint32_t g;
-    bool bad = false;
-    KeyT k = (KeyT)ks.dead;
-    if (event_live(e, idents, n_idents, &g, &bad)) k = (KeyT)lsg_make_key(ks, g, e.ts);
-    keys[i] = k;
+    uint64_t k = ks.dead;
+    event_key(e, idents, n_idents, ks, tally, &k);
+    keys[i] = (KeyT)k;
   }
+  tally.flush(st);
 }
 
 template <typename KeyT>
@@ -333,8 +367,9 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
 
 __global__ void __launch_bounds__(256)
 k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n,
-                lsg_event *__restrict__ sorted) {
+                const uint32_t *__restrict__ n_placed, lsg_event *__restrict__ sorted) {
   // one 256-bit load and one 256-bit store per record; four records in flight per thread
+  if (n_placed) n = min(n, (size_t)*n_placed);   // counting sort: only the live events have a permutation entry
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; j + 3 * stride < n; j += 4 * stride) {
@@ -349,9 +384,11 @@ k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict
 
 // the same gather into columns: what the join stages into shared memory (ts, ident, pid, conn, trace|signal) plus values
 __global__ void __launch_bounds__(256)
-k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n, int64_t *__restrict__ ts,
+k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n,
+                    const uint32_t *__restrict__ n_placed, int64_t *__restrict__ ts,
                     double *__restrict__ val, uint32_t *__restrict__ ident, uint32_t *__restrict__ pid,
                     uint32_t *__restrict__ conn, uint32_t *__restrict__ trsig) {
+  if (n_placed) n = min(n, (size_t)*n_placed);   // counting sort: only the live events have a permutation entry
   auto put = [&](const size_t j, const U8 r) {
     ts[j] = (int64_t)(((uint64_t)r.a.y << 32) | r.a.x);
     val[j] = __longlong_as_double((long long)(((uint64_t)r.a.w << 32) | r.a.z));
@@ -385,8 +422,9 @@ constexpr uint32_t COUNTING_MAX_KEYS = 1u << 25;   // 128 MB of counters at most
 // rank are kept (8 B/event) so that the placement below neither repeats the atomic nor reads the records again.
 __global__ void __launch_bounds__(256)
 k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents,
-             KeySpec ks, uint32_t *__restrict__ bins, uint2 *__restrict__ key_rank) {
+             KeySpec ks, uint32_t *__restrict__ bins, uint2 *__restrict__ key_rank, EventStats *st) {
   // the returning atomic has L2 round-trip latency: four events per thread in flight
+  EventTally tally;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; i + 3 * stride < n; i += 4 * stride) {
@@ -396,10 +434,9 @@ k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
     for (int u = 0; u < 4; ++u) e[u] = load_event(events + i + u * stride);
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      uint32_t g;
-      bool bad = false;
+      uint64_t k;
       kr[u] = make_uint2(0xffffffffu, 0u);   // not placed: matches nothing
-      if (event_live(e[u], idents, n_idents, &g, &bad)) kr[u].x = (uint32_t)lsg_make_key(ks, g, e[u].ts);
+      if (event_key(e[u], idents, n_idents, ks, tally, &k)) kr[u].x = (uint32_t)k;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u)
@@ -409,15 +446,15 @@ k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
   }
   for (; i < n; i += stride) {
     const EventRec e = load_event(events + i);
-    uint32_t g;
-    bool bad = false;
+    uint64_t k;
     uint2 kr = make_uint2(0xffffffffu, 0u);
-    if (event_live(e, idents, n_idents, &g, &bad)) {
-      kr.x = (uint32_t)lsg_make_key(ks, g, e.ts);
+    if (event_key(e, idents, n_idents, ks, tally, &k)) {
+      kr.x = (uint32_t)k;
       kr.y = atomicAdd(&bins[kr.x], 1u);
     }
     key_rank[i] = kr;
   }
+  tally.flush(st);
 }
 
 // pass 3 (after the scan turned the counts into run starts): position = start of the key's run + rank.
@@ -636,17 +673,17 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
   EventStats *pin = (EventStats *)ctx->pinned;
   *pin = init;
   LSG_CUDA(ctx, cudaMemcpyAsync(st_dev, pin, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  const bool from_spans = spans != nullptr && n_spans != 0;
   {
   ProfScope ps_stats(ctx, PK_STATS);
   if (n_idents) {
     k_ident_stats<<<grid_for(ctx, n_idents, 256, 1), 256, 0, ctx->stream>>>(idents, (uint32_t)n_idents, st_dev);
     LSG_LAUNCH_CHECK(ctx);
   }
-  if (spans && n_spans) {
-    k_span_check<<<grid_for(ctx, n_spans, 256, 8), 256, 0, ctx->stream>>>(spans, n_spans, (uint32_t)n_idents, st_dev);
+  if (from_spans) {
+    k_span_stats<<<grid_for(ctx, n_spans, 256, 8), 256, 0, ctx->stream>>>(spans, n_spans, idents, (uint32_t)n_idents, st_dev);
     LSG_LAUNCH_CHECK(ctx);
-  }
-  if (n) {
+  } else if (n) {
     k_event_stats<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, st_dev);
     LSG_LAUNCH_CHECK(ctx);
   }
@@ -656,11 +693,28 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
   EventStats st = *pin;
   if (st.bad & 1u) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
   if (st.bad & 2u) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
-  out->n_live = st.n_live;
-  out->n_unsupported = st.n_unsupported;
+  out->stats_dev = st_dev;
+  out->tally_in_sort = from_spans;
   KeySpec ks;
-  ks.ts_min = st.n_live ? st.ts_min : 0;
-  const uint64_t range = st.n_live ? (uint64_t)st.ts_max - (uint64_t)st.ts_min : 0;
+  uint64_t range = 0;
+  if (from_spans) {
+    // the events are not read before the sort: its first pass counts the unsupported types and checks the idents.
+    // An event further than the window from every live span can match nothing, so the time axis is the spans'.
+    out->n_live = n;
+    if (st.ts_min <= st.ts_max) {
+      ks.ts_min = st.ts_min < INT64_MIN + window_ns ? INT64_MIN : st.ts_min - window_ns;
+      ks.ts_hi = st.ts_max > INT64_MAX - window_ns ? INT64_MAX : st.ts_max + window_ns;
+      range = (uint64_t)ks.ts_hi - (uint64_t)ks.ts_min;
+    } else {
+      ks.ts_min = 0;    // no span can match: every event is dead
+      ks.ts_hi = -1;
+    }
+  } else {
+    out->n_live = st.n_live;
+    ks.ts_min = st.n_live ? st.ts_min : 0;
+    ks.ts_hi = st.n_live ? st.ts_max : -1;
+    range = st.n_live ? (uint64_t)st.ts_max - (uint64_t)st.ts_min : 0;
+  }
   ks.shift = 0;
   if (!exact) {
     // largest quantum <= window/32 (measured optimum on C2: halves the bin table for ~3% more inner-range events)
@@ -685,6 +739,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
                            lsg_event *sorted_out, SortedEvents *out, bool allow_counting) {
   const KeySpec ks = out->key;
   if (n == 0) return 0;
+  EventStats *tally_dst = out->tally_in_sort ? const_cast<EventStats *>(out->stats_dev) : nullptr;
   // where the events go: the caller's record array, or columns in the workspace (padded so that a 16-byte aligned
   // bulk copy may run a little past the last event)
   int64_t *c_ts = nullptr; double *c_val = nullptr; uint32_t *c_ident = nullptr, *c_pid = nullptr, *c_conn = nullptr, *c_trsig = nullptr;
@@ -701,10 +756,10 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
   } else {
     out->rec = sorted_out;
   }
-  auto gather = [&](const uint32_t *perm, size_t count) -> int {
+  auto gather = [&](const uint32_t *perm, size_t count, const uint32_t *n_placed) -> int {
     ProfScope ps(ctx, PK_GATHER);
-    if (sorted_out) k_gather_events<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, sorted_out);
-    else k_gather_events_soa<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
+    if (sorted_out) k_gather_events<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, n_placed, sorted_out);
+    else k_gather_events_soa<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, n_placed, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
     LSG_LAUNCH_CHECK(ctx);
     return 0;
   };
@@ -721,7 +776,8 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
     {
       ProfScope ps(ctx, PK_HIST);
       LSG_CUDA(ctx, cudaMemsetAsync(bins, 0, n_keys * 4, ctx->stream));
-      k_count_keys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, bins, key_rank);
+      k_count_keys<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, bins, key_rank,
+                                                                      tally_dst);
       LSG_LAUNCH_CHECK(ctx);
     }
     {
@@ -738,7 +794,8 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
       k_place_events<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(key_rank, n, bins, perm);
       LSG_LAUNCH_CHECK(ctx);
     }
-    if (out->n_live) LSG_TRY(gather(perm, out->n_live));
+    // after the scan bins[dead] is the start of the (empty) dead run: the number of events that were placed
+    if (out->n_live) LSG_TRY(gather(perm, out->n_live, bins + ks.dead));
     out->bins = bins;
     out->perm = perm;
     return 0;
@@ -753,7 +810,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
   if (k32) {
     {
       ProfScope ps(ctx, PK_KEYS);
-      k_event_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint32_t *)ka);
+      k_event_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint32_t *)ka, tally_dst);
       LSG_LAUNCH_CHECK(ctx);
     }
     uint32_t *ko;
@@ -762,7 +819,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
   } else {
     {
       ProfScope ps(ctx, PK_KEYS);
-      k_event_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint64_t *)ka);
+      k_event_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(events, n, idents, (uint32_t)n_idents, ks, (uint64_t *)ka, tally_dst);
       LSG_LAUNCH_CHECK(ctx);
     }
     uint64_t *ko;
@@ -770,7 +827,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
     out->keys = ko;
   }
   out->perm = perm;
-  return gather(perm, n);
+  return gather(perm, n, nullptr);
 }
 
 // Processing order of the spans: same key as the events, so consecutive spans read overlapping event ranges.

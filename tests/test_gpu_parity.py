@@ -85,6 +85,45 @@ def test_counted_tier4_with_empty_service_or_node(ctx):
         _eq_batch(got, want)
 
 
+def test_key_range_comes_from_the_spans(ctx):
+    """The time axis of the sort is the spans' range widened by the window: events far outside it (clock glitches,
+    a replay file that holds a whole day) match nothing, do not widen the key space and still count as unmatched."""
+    cfg = synth.config(150_000, 15_000, 16, 8, 2, seed=31, horizon_ns=30_000_000_000)
+    w = synth.generate_host(cfg)
+    ev = w["events"].copy()
+    rng = np.random.default_rng(3)
+    far = rng.choice(len(ev), 3000, replace=False)
+    ev["ts_ns"][far[:1000]] += 400 * 86400 * 10**9          # more than a year later
+    ev["ts_ns"][far[1000:2000]] -= 10 * 86400 * 10**9         # ten days earlier
+    ev["ts_ns"][far[2000:2500]] = (1 << 62)
+    ev["ts_ns"][far[2500:]] = -(1 << 62)
+    got = ctx.process_batch(w["spans"], ev, w["idents"])
+    want = O.process_batch(w["spans"], ev, w["idents"], indexed=True, nthreads=8)
+    _eq_batch(got, want)
+    info = ctx.last_sort_info()
+    assert info["key_bits"] <= 25, info                       # 30 s of spans + 2 x 2 s, not 400 days
+    # events exactly one window before the first / after the last span still match; one nanosecond further they do not
+    sp = w["spans"][:2000].copy()
+    t_lo, t_hi = int(sp["ts_ns"].min()), int(sp["ts_ns"].max())
+    W = 2_000_000_000
+    edge = w["events"][:4000].copy()
+    first, last = int(np.argmin(sp["ts_ns"])), int(np.argmax(sp["ts_ns"]))
+    for k, (src, t) in enumerate(((first, t_lo - W), (first, t_lo - W - 1), (last, t_hi + W), (last, t_hi + W + 1))):
+        edge["ts_ns"][k] = t
+        edge["ident"][k] = sp["ident"][src]
+        edge["trace_sig"][k] = (int(sp["trace"][src]) << 4) | 0
+    got = ctx.process_batch(sp, edge, w["idents"])
+    want = O.process_batch(sp, edge, w["idents"], indexed=False, nthreads=8)
+    _eq_batch(got, want)
+    # no span can match at all: nothing is kept, every supported pair is unmatched
+    dead = sp.copy()
+    dead["ts_ns"][:] = A.TS_ZERO
+    got = ctx.process_batch(dead, edge, w["idents"])
+    want = O.process_batch(dead, edge, w["idents"], indexed=False, nthreads=8)
+    _eq_batch(got, want)
+    assert (got["cand_event"] == A.NONE).all()
+
+
 def test_brute_force_subsample(ctx):
     """the literal O(S x E) restatement of the reference loop on a sub-sample"""
     cfg = synth.config(50_000, 2_000, 16, 8, 2, seed=5, horizon_ns=10_000_000_000)
@@ -432,6 +471,17 @@ def test_host_pipeline_blocking_and_double_buffered(ctx):
     assert e.value.code == -4
     with pytest.raises(pkg.LsgError) as e:
         ctx.process_batch(w_bad["spans"], w_bad["events"], w_bad["idents"])
+    assert e.value.code == -4
+    w_bad = dict(batches[0][1])                           # the same for an event
+    w_bad["events"] = w_bad["events"].copy()
+    w_bad["events"]["ident"][5] = 1 << 30
+    args, keep, outs = host_args(w_bad)
+    with pytest.raises(pkg.LsgError) as e:
+        ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(A.Counters()))
+    assert e.value.code == -4
+    ctx.call_dev("lsg_pipeline_submit", C.byref(args), 0)
+    with pytest.raises(pkg.LsgError) as e:
+        ctx.call_dev("lsg_pipeline_wait", 0, C.byref(A.Counters()))
     assert e.value.code == -4
     args, keep, outs = host_args(batches[1][1])           # and the context is usable afterwards
     c = A.Counters()
