@@ -10,19 +10,25 @@
 // index); every lane keeps its best F under that order and the warp merges them, so neither the scan
 // order nor the time quantisation can change the result.
 //
-// Two kernels:
+// Kernels:
 //   k_span_ranges  one thread per span (in key order): its outer range [a, b) (|dt| <= W, the only place a
-//                  trace-id match can be) and inner range [a2, b2) (|dt| <= min(W, 500 ms), the only place
-//                  tiers 2-4 can be): two reads of the counting sort's bin table, or binary searches in the
+//                  trace-id match can be), its inner range [a2, b2) (|dt| <= min(W, 500 ms), the only place
+//                  tiers 2-4 can be), the whole time quanta inside the exact inner window and the +-250 ms part
+//                  of the inner range: reads of the counting sort's bin table, or binary searches in the
 //                  sorted keys on the radix path.
+//   k_ident_class_*  per identity row (pod, class of its (service, node) pair), so that a (span, event) pair
+//                  compares two words instead of loading two identity rows.
 //   k_join_tiles   a CTA takes 128 consecutive spans.  Their ranges overlap heavily (each event is inside
 //                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — five columns,
-//                  24 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier).
-//                  Tier 1 is a tile-local hash join (every tile event probes a hash of the chunk's span trace
-//                  ids once); tiers 2-4 are decided by two threads per span walking the span's inner range
-//                  out of shared memory; matches are noted in two bytes and ordered afterwards in registers.
+//                  24 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier) and
+//                  rewrites the identity column to (pod, class) in place.  Tier 1 is a tile-local hash join
+//                  (every tile event probes a hash of the chunk's span trace ids once).  Tiers 2-4 are decided
+//                  by two threads per span out of shared memory; where every event of the tile carries one
+//                  class and the service+node tier is below the threshold, that tier is counted (whole quanta
+//                  + exact edge tests - trace-id matches - tier 2/3 matches) and only the +-250 ms part is
+//                  enumerated.  Matches are noted in two bytes and ordered afterwards in registers.
 //   k_join_big     the spans the tile kernel leaves out (range larger than a tile, overflowing note list, time
-//                  outside the events' range, fanout > 8): one warp per span straight from global memory.
+//                  outside the key space, fanout > 8): one warp per span straight from global memory.
 // Outputs are written at the span's input position; optionally the per-incident maxima (A7 glue) are
 // accumulated from the epilogue with one atomicMax per present attribute.
 #include <algorithm>
@@ -35,7 +41,6 @@ namespace {
 constexpr int JT_THREADS = 256;
 constexpr int JT_WARPS = JT_THREADS / 32;
 constexpr int JT_CH = 128;     // spans per chunk
-constexpr int JT_CAP = 2048;   // events per shared-memory tile
 
 struct JoinParams {
   const lsg_span *spans;
