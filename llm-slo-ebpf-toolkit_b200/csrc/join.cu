@@ -697,64 +697,71 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
       n_unlisted += __shfl_down_sync(0xffffffffu, n_unlisted, 1);
       n_cand += n_unlisted;   // candidates that were counted without being noted
-      // ---- write: the even lane owns the span
-      if (live && !h) {
+      // ---- write: the even lane owns the span's candidates, confidence and counters; the twelve attribute columns
+      //      are split between the two lanes (six each), which both read the kept candidates' values and signals
+      if (live) {
         if (redo) {
-          big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q0 + k);   // more candidates than the list holds
+          if (!h) big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q0 + k);   // more candidates than the list holds
         } else {
+          const unsigned pair = 3u << (lane & 30u);
           const size_t si = sm.sidx[k];
-          const uint32_t n_tr = sm.n_tr[k];
-          n_match += n_tr;
-          if (cut < 1) n_low += n_tr;
           double vals[F];
           unsigned sigs[F];
+          unsigned present = 0;
           int kept = 0;
 #pragma unroll
           for (int r = 0; r < F; ++r) {
-            const bool has = r < p.fanout && top.idx[r] != 0xffffffffu;
-            vals[r] = has ? p.ev.val[top.pos[r]] : 0.0;
-            sigs[r] = has ? (sm.trsig[top.pos[r] - A] & 15u) : 0xffu;
+            const bool mine = r < p.fanout && top.idx[r] != 0xffffffffu;
+            const uint32_t pos = __shfl_sync(pair, mine ? top.pos[r] : 0xffffffffu, lane & 30u);   // the even lane's final list
+            const bool has = pos != 0xffffffffu;
+            vals[r] = has ? p.ev.val[pos] : 0.0;
+            sigs[r] = has ? (sm.trsig[pos - A] & 15u) : 0xffu;
             kept += has;
-            if (r < p.fanout) {
+            present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
+            if (!h && r < p.fanout) {
               p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
               p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
             }
           }
           // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
           double v0 = nan, v3 = nan, v4 = nan;
-          unsigned present = 0;
+          const bool to_incident = p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents;
 #pragma unroll
-          for (int r = 0; r < F; ++r) present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
-#pragma unroll
-          for (int col = 0; col < LSG_NSIG; ++col) {
+          for (int c = 0; c < LSG_NSIG / 2; ++c) {
+            const unsigned col = h * (LSG_NSIG / 2) + c;
             double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
             if ((present >> col) & 1u) {
 #pragma unroll
               for (int r = 0; r < F; ++r)
-                if (sigs[r] == (unsigned)col && (isnan(v) || vals[r] > v)) v = vals[r];
+                if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
             }
             p.attr_out[si * LSG_NSIG + col] = v;
-            if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(v))
+            if (to_incident && !isnan(v))
               atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
-            if (col == 0) v0 = v;
-            if (col == 3) v3 = v;
-            if (col == 4) v4 = v;
+            if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
+            if (c == 3) v3 = v;
+            if (c == 4) v4 = v;
           }
-          // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
-          p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
-          if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
-            double total = 0.0;
-            if (!isnan(v0)) total += v0;
-            if (!isnan(v3)) total += v3;
-            if (!isnan(v4)) total += v4;
-            p.retrieval_out[si] = total;
+          if (!h) {
+            const uint32_t n_tr = sm.n_tr[k];
+            n_match += n_tr;
+            if (cut < 1) n_low += n_tr;
+            // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
+            p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
+            if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
+              double total = 0.0;
+              if (!isnan(v0)) total += v0;
+              if (!isnan(v3)) total += v3;
+              if (!isnan(v4)) total += v4;
+              p.retrieval_out[si] = total;
+            }
+            if (p.n_cand_out) p.n_cand_out[si] = n_cand;
+            w_matched += n_match;
+            w_low += n_low;
+            w_cand += n_cand;
+            w_kept += kept;
+            if (n_cand > (uint32_t)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
           }
-          if (p.n_cand_out) p.n_cand_out[si] = n_cand;
-          w_matched += n_match;
-          w_low += n_low;
-          w_cand += n_cand;
-          w_kept += kept;
-          if (n_cand > (uint32_t)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
         }
       }
       __syncthreads();   // every thread is done with the tile before the next bulk copy overwrites it
