@@ -368,16 +368,16 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
 __global__ void __launch_bounds__(256)
 k_gather_events(const lsg_event *__restrict__ events, const uint32_t *__restrict__ perm, size_t n,
                 const uint32_t *__restrict__ n_placed, lsg_event *__restrict__ sorted) {
-  // one 256-bit load and one 256-bit store per record; four records in flight per thread
+  // one 256-bit load and one 256-bit store per record; eight records in flight per thread
   if (n_placed) n = min(n, (size_t)*n_placed);   // counting sort: only the live events have a permutation entry
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  for (; j + 3 * stride < n; j += 4 * stride) {
-    U8 r[4];
+  for (; j + 7 * stride < n; j += 8 * stride) {
+    U8 r[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
+    for (int u = 0; u < 8; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) st_v8(sorted + j + u * stride, r[u]);
+    for (int u = 0; u < 8; ++u) st_v8(sorted + j + u * stride, r[u]);
   }
   for (; j < n; j += stride) st_v8(sorted + j, ld_nc_v8(events + perm[j]));
 }
@@ -397,15 +397,15 @@ k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__rest
     conn[j] = r.b.z;
     trsig[j] = r.b.w;
   };
-  // one 256-bit load per record, four records in flight per thread; the column stores are coalesced
+  // one 256-bit load per record, eight records in flight per thread; the column stores are coalesced
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  for (; j + 3 * stride < n; j += 4 * stride) {
-    U8 r[4];
+  for (; j + 7 * stride < n; j += 8 * stride) {
+    U8 r[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
+    for (int u = 0; u < 8; ++u) r[u] = ld_nc_v8(events + perm[j + u * stride]);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) put(j + u * stride, r[u]);
+    for (int u = 0; u < 8; ++u) put(j + u * stride, r[u]);
   }
   for (; j < n; j += stride) put(j, ld_nc_v8(events + perm[j]));
 }
