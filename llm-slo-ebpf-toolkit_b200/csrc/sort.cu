@@ -54,14 +54,29 @@ k_span_stats(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__re
     tmin = min(tmin, (long long)s.ts);
     tmax = max(tmax, (long long)s.ts);
   }
+  // warp -> block -> one pair of atomics per block (every warp hitting the same two words serialises in L2)
+  __shared__ long long s_min[8], s_max[8];
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
   for (int o = 16; o; o >>= 1) {
     tmin = min(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
     tmax = max(tmax, __shfl_xor_sync(0xffffffffu, tmax, o));
   }
-  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&st->bad, 2u);
-  if ((threadIdx.x & 31) == 0 && tmin <= tmax) {
-    atomicMin(&st->ts_min, tmin);
-    atomicMax(&st->ts_max, tmax);
+  const bool warp_bad = __any_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0) {
+    s_min[threadIdx.x >> 5] = tmin;
+    s_max[threadIdx.x >> 5] = tmax;
+    if (warp_bad) s_bad = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { tmin = min(tmin, s_min[w]); tmax = max(tmax, s_max[w]); }
+    if (s_bad) atomicOr(&st->bad, 2u);
+    if (tmin <= tmax) {
+      atomicMin(&st->ts_min, tmin);
+      atomicMax(&st->ts_max, tmax);
+    }
   }
 }
 

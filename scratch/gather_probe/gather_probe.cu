@@ -45,21 +45,78 @@ __device__ __forceinline__ Rec ld_evict_first(const Rec *p) {
   return r;
 }
 
+__device__ __forceinline__ Rec ld_l2_64(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.L2::64B.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+  asm volatile("ld.global.L2::64B.v2.u64 {%0,%1}, [%2+16];" : "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ Rec ld_l2_128(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.L2::128B.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+  asm volatile("ld.global.L2::128B.v2.u64 {%0,%1}, [%2+16];" : "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ Rec ld_l2_256(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.L2::256B.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+  asm volatile("ld.global.L2::256B.v2.u64 {%0,%1}, [%2+16];" : "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ Rec ld_nc_l2_64(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.nc.L2::64B.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+  asm volatile("ld.global.nc.L2::64B.v2.u64 {%0,%1}, [%2+16];" : "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ Rec ld_256_l2_64(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r.a), "=l"(r.b), "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ Rec ld_nc256_l2_64(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::64B.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r.a), "=l"(r.b), "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ Rec ld_plain2(const Rec *p) {
+  Rec r;
+  asm volatile("ld.global.v2.u64 {%0,%1}, [%2];" : "=l"(r.a), "=l"(r.b) : "l"(p));
+  asm volatile("ld.global.v2.u64 {%0,%1}, [%2+16];" : "=l"(r.c), "=l"(r.d) : "l"(p));
+  return r;
+}
+
 template <int V>
+__device__ __forceinline__ Rec ld_variant(const Rec *p) {
+  if (V == 10) return ld_nc_l2_64(p);
+  if (V == 11) return ld_256_l2_64(p);
+  if (V == 12) return ld_nc256_l2_64(p);
+  if (V == 13) return ld_plain2(p);
+  if (V == 0) return ld_nc256(p);
+  if (V == 1) return ld_2x128(p);
+  if (V == 2) return ld_cg(p);
+  if (V == 3) return ld_cv(p);
+  if (V == 4) return ld_lu(p);
+  if (V == 5) return ld_evict_first(p);
+  if (V == 6) return ld_l2_64(p);
+  if (V == 7) return ld_l2_128(p);
+  if (V == 8) return ld_l2_256(p);
+  return *p;
+}
+
+template <int V, int ILP = 1>
 __global__ void __launch_bounds__(256) k_gather(const Rec *__restrict__ in, const uint32_t *__restrict__ perm, size_t n, Rec *__restrict__ out) {
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const Rec *p = in + perm[i];
-    Rec r;
-    if (V == 0) r = ld_nc256(p);
-    else if (V == 1) r = ld_2x128(p);
-    else if (V == 2) r = ld_cg(p);
-    else if (V == 3) r = ld_cv(p);
-    else if (V == 4) r = ld_lu(p);
-    else if (V == 5) r = ld_evict_first(p);
-    else r = *p;
-    out[i] = r;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + (ILP - 1) * stride < n; i += ILP * stride) {
+    Rec r[ILP];
+#pragma unroll
+    for (int u = 0; u < ILP; ++u) r[u] = ld_variant<V>(in + perm[i + u * stride]);
+#pragma unroll
+    for (int u = 0; u < ILP; ++u) out[i + u * stride] = r[u];
   }
+  for (; i < n; i += stride) out[i] = ld_variant<V>(in + perm[i]);
 }
 
 // TMA-style bulk copies: each thread pulls its 32-byte record into shared memory with cp.async.bulk, then writes it out
@@ -132,5 +189,18 @@ int main(int argc, char **argv) {
   run("ld.L2::evict_first.v4.u64", [&] { k_gather<5><<<grid, 256>>>(in, dperm, n, out); });
   run("plain struct load", [&] { k_gather<9><<<grid, 256>>>(in, dperm, n, out); });
   run("cp.async.bulk 32 B", [&] { k_gather_bulk<<<grid, 256>>>(in, dperm, n, out); });
+  run("nc256, 4 in flight", [&] { k_gather<0, 4><<<grid, 256>>>(in, dperm, n, out); });
+  run("nc256, 8 in flight", [&] { k_gather<0, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("nc256, 16 in flight", [&] { k_gather<0, 16><<<grid, 256>>>(in, dperm, n, out); });
+  run("L2::64B, 8 in flight", [&] { k_gather<6, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("L2::128B, 8 in flight", [&] { k_gather<7, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("L2::256B, 8 in flight", [&] { k_gather<8, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("nc L2::64B 2x128, 8 in flight", [&] { k_gather<10, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("L2::64B v4.u64, 8 in flight", [&] { k_gather<11, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("nc.noalloc.L2::64B v4, 8", [&] { k_gather<12, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("plain 2x128, 8 in flight", [&] { k_gather<13, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("L2::64B 2x128, 1 in flight", [&] { k_gather<6, 1><<<grid, 256>>>(in, dperm, n, out); });
+  run("evict_first, 8 in flight", [&] { k_gather<5, 8><<<grid, 256>>>(in, dperm, n, out); });
+  run("nc256, 8 in flight, 4 CTA/SM", [&] { k_gather<0, 8><<<148 * 4, 256>>>(in, dperm, n, out); });
   return 0;
 }
