@@ -130,7 +130,10 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
     if (rc) return rc;
     LSG_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->side));
   }
-  LSG_TRY(lsg_sort_events_finish(ctx, events, n_events, idents, n_idents, nullptr, sorted, true));
+  // the join gathers its own tiles through the permutation: no sorted copy of the events (LSG_JOIN_SORTED_COPY=1
+  // keeps the separate gather pass, for comparison)
+  static const bool sorted_copy = getenv("LSG_JOIN_SORTED_COPY") != nullptr;
+  LSG_TRY(lsg_sort_events_finish(ctx, events, n_events, idents, n_idents, nullptr, sorted, true, sorted_copy));
   LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
   void *small_v;
   LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));

@@ -289,8 +289,9 @@ int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_iden
 // Without spans (the sort as its own entry point) one pass over the events sets the range.
 int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                             int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans);
+// want_copy false (and sorted_out NULL): only the permutation (and bins / keys) is produced, no sorted copy of the events
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting);
+                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting, bool want_copy);
 int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, uint32_t sig,
                            const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out, size_t *n_live_out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,

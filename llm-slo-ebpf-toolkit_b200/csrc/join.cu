@@ -46,7 +46,8 @@ struct JoinParams {
   const lsg_span *spans;
   const uint32_t *span_perm;
   size_t n_spans;
-  EventColumns ev;
+  EventColumns ev;           // events in key order as columns; all NULL when no sorted copy was made (FUSED kernels)
+  const lsg_event *events_in;   // the input records (what ev_perm indexes)
   const uint32_t *ev_perm;   // sorted position -> input index
   const uint4 *ranges;       // per span in key order: outer [x, y) and inner [z, w) in sorted positions
   const uint4 *ranges2;      // whole-quanta core [x, y) of the inner window and the +-250 ms part [z, w) of the inner range
@@ -191,11 +192,41 @@ struct Cand {
   uint32_t pos;   // sorted position of the event
 };
 
-// the columns a scan reads, either the shared-memory tile (base = first staged position) or global memory (base 0)
-struct Cols {
-  const int64_t *ts;
-  const uint32_t *ident, *pid, *conn, *trsig, *perm;
-  uint32_t base;
+// What the warp-per-span scan reads: the events in key order, either as the sorted columns or, when no sorted copy
+// was made (the tile kernel gathers its own tiles), as the input records behind the permutation.
+struct ColsSorted {
+  const int64_t *ts_;
+  const double *val_;
+  const uint32_t *ident_, *pid_, *conn_, *trsig_, *perm_;
+  __device__ __forceinline__ int64_t ts(uint32_t o) const { return ts_[o]; }
+  __device__ __forceinline__ double val(uint32_t o) const { return val_[o]; }
+  __device__ __forceinline__ uint32_t ident(uint32_t o) const { return ident_[o]; }
+  __device__ __forceinline__ uint32_t pid(uint32_t o) const { return pid_[o]; }
+  __device__ __forceinline__ uint32_t conn(uint32_t o) const { return conn_[o]; }
+  __device__ __forceinline__ uint32_t trsig(uint32_t o) const { return trsig_[o]; }
+  __device__ __forceinline__ uint32_t perm(uint32_t o) const { return perm_[o]; }
+  // four consecutive trace|signal words, o a multiple of 4 (the columns are padded past the last event)
+  __device__ __forceinline__ uint4 trsig4(uint32_t o, uint32_t) const { return *reinterpret_cast<const uint4 *>(trsig_ + o); }
+};
+struct ColsIndirect {
+  const lsg_event *ev_;
+  const uint32_t *perm_;
+  __device__ __forceinline__ const lsg_event *at(uint32_t o) const { return ev_ + perm_[o]; }
+  __device__ __forceinline__ int64_t ts(uint32_t o) const { return at(o)->ts_ns; }
+  __device__ __forceinline__ double val(uint32_t o) const { return at(o)->value; }
+  __device__ __forceinline__ uint32_t ident(uint32_t o) const { return at(o)->ident; }
+  __device__ __forceinline__ uint32_t pid(uint32_t o) const { return at(o)->pid; }
+  __device__ __forceinline__ uint32_t conn(uint32_t o) const { return at(o)->conn; }
+  __device__ __forceinline__ uint32_t trsig(uint32_t o) const { return at(o)->trace_sig; }
+  __device__ __forceinline__ uint32_t perm(uint32_t o) const { return perm_[o]; }
+  __device__ __forceinline__ uint4 trsig4(uint32_t o, uint32_t end) const {   // positions at or past `end` are not looked at
+    uint4 q = make_uint4(0, 0, 0, 0);
+    if (o < end) q.x = trsig(o);
+    if (o + 1 < end) q.y = trsig(o + 1);
+    if (o + 2 < end) q.z = trsig(o + 2);
+    if (o + 3 < end) q.w = trsig(o + 3);
+    return q;
+  }
 };
 
 __device__ __forceinline__ bool cand_less(uint64_t ka, uint32_t ia, uint64_t kb, uint32_t ib) {
@@ -235,6 +266,7 @@ __device__ __forceinline__ int select_best(const Cand *list, const int n, const 
 }
 
 // One span, one warp: scan, select, write.  Counters go to the caller's per-lane accumulators.
+template <typename Cols>
 __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, Cand *list, const SpanRec s, const size_t si,
                                              const uint4 rg_in, const unsigned lane, unsigned long long &w_matched,
                                              unsigned long long &w_low, unsigned long long &w_drop, unsigned long long &w_cand,
@@ -261,7 +293,7 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
       n_list = kept;
       __syncwarp();
     }
-    if (has) list[n_list + __popc(m & lt_mask)] = Cand{k1, c.perm[o], j};
+    if (has) list[n_list + __popc(m & lt_mask)] = Cand{k1, c.perm(o), j};
     n_list += __popc(m);
     n_cand += __popc(m);   // warp-uniform running total
   };
@@ -270,11 +302,11 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
     // ---- tier 1 (dns.go:58-60): a trace-id match can sit anywhere in the outer window.  Only the trace|signal
     //      column is read, four events per lane and load; the time is looked at for hits only.
     if (s.trace != 0) {
-      const uint32_t v0 = (rg.x - c.base) & ~3u, v_end = rg.y - c.base, v_beg = rg.x - c.base;
+      const uint32_t v0 = rg.x & ~3u, v_end = rg.y, v_beg = rg.x;
       for (uint32_t vb = v0; vb < v_end; vb += 128) {
         const uint32_t v = vb + lane * 4;
         uint4 q = make_uint4(0, 0, 0, 0);
-        if (v < v_end) q = *reinterpret_cast<const uint4 *>(c.trsig + v);   // 16-byte aligned; the tile is padded past its end
+        if (v < v_end) q = c.trsig4(v, v_end);
         const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -282,14 +314,14 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
           bool hit = o >= v_beg && o < v_end && (w[e] >> 4) == s.trace;
           uint64_t adt = 0;
           if (hit) {
-            adt = lsg_absdiff(s.ts, c.ts[o]);
+            adt = lsg_absdiff(s.ts, c.ts(o));
             hit = adt <= W;                                   // outer window, dns.go:54-56
           }
           if (__any_sync(0xffffffffu, hit)) {
             n_match += __popc(__ballot_sync(0xffffffffu, hit));
             const bool low = hit && 1.0 < p.threshold;       // confidence 1.0 below the threshold (threshold > 1)
             n_low += __popc(__ballot_sync(0xffffffffu, low));
-            append(hit && !low, ((uint64_t)LSG_TIER_TRACE << 56) | adt, o, o + c.base);
+            append(hit && !low, ((uint64_t)LSG_TIER_TRACE << 56) | adt, o, o);
           }
         }
       }
@@ -304,14 +336,14 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
         uint64_t adt = 0;
         uint32_t o = 0;
         if (j < rg.w) {
-          o = j - c.base;
-          adt = lsg_absdiff(s.ts, c.ts[o]);
-          const uint32_t trsig = c.trsig[o];
+          o = j;
+          adt = lsg_absdiff(s.ts, c.ts(o));
+          const uint32_t trsig = c.trsig(o);
           if (adt <= Wi && !(s.trace != 0 && s.trace == (trsig >> 4))) {
-            const uint32_t e_ident = c.ident[o];
+            const uint32_t e_ident = c.ident(o);
             lsg_ident eid = sid;
             if (e_ident != s.ident) eid = load_ident(p.idents, e_ident);
-            tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, c.pid[o], c.conn[o], eid);
+            tier = lsg_match_tier(adt, 0, s.pid, s.conn, sid, 0, c.pid(o), c.conn(o), eid);
           }
         }
         const bool is_m = tier != 0;
@@ -342,8 +374,8 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
   double my_val = 0.0;
   unsigned my_sig = 0xffu;
   if ((int)lane < kept) {
-    my_val = p.ev.val[my_pos];
-    my_sig = p.ev.trsig[my_pos] & 15u;
+    my_val = c.val(my_pos);
+    my_sig = c.trsig(my_pos) & 15u;
   }
   for (int r = 0; r < kept; ++r) {
     const double v = __shfl_sync(0xffffffffu, my_val, r);
@@ -446,7 +478,9 @@ struct TileSmem {
 
 __device__ __forceinline__ uint32_t trace_slot(uint32_t tr) { return (tr * 2654435761u) >> 24; }   // 8 bits
 
-template <int F, bool T32>
+// FUSED: there is no sorted copy of the events; the CTA gathers its tile's records through the permutation itself
+// (random 32-byte reads, issued four deep per thread), writing the columns and the (pod, class) words in one go.
+template <int F, bool T32, bool FUSED>
 __global__ void __launch_bounds__(JT_THREADS, 3)
 k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -517,7 +551,44 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       const int i1 = i0 + n_fit;
       const uint32_t Bend = (sm.rng[i1 - 1].y + 3u) & ~3u;
       const uint32_t count = Bend > A ? Bend - A : 0;   // <= TM_CAP, multiple of 4; the columns are padded past n
-      if (count) {
+      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
+      const uint32_t live_beg = sm.rng[i0].x - A, live_end = min(count, sm.rng[i1 - 1].y - A);
+      uint32_t cmin = 0xffffffffu, cmax = 0u;
+      if (FUSED) {
+        // every thread gathers its share of the tile (at most TM_CAP / JT_THREADS = 7 records): first all its
+        // permutation entries (coalesced), then the records four at a time as independent 256-bit loads
+        constexpr int PER = (TM_CAP + JT_THREADS - 1) / JT_THREADS;
+        uint32_t src[PER];
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+          const uint32_t o = tid + u * JT_THREADS;
+          src[u] = o < live_end ? __ldg(p.ev_perm + A + o) : 0xffffffffu;
+        }
+#pragma unroll
+        for (int ub = 0; ub < PER; ub += 4) {
+          U8 r[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            r[u].a = make_uint4(0, 0, 0, 0);
+            r[u].b = make_uint4(0xffffffffu, 0, 0, 0);   // padding: an identity row no table has
+            if (ub + u < PER && src[ub + u] != 0xffffffffu) r[u] = ld_nc_v8(p.events_in + src[ub + u]);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const uint32_t o = tid + (ub + u) * JT_THREADS;
+            if (ub + u >= PER || o >= count) continue;
+            const uint32_t row = r[u].b.x;
+            const uint2 pc = row < p.n_idents ? __ldg(p.ident_pc + row) : make_uint2(0u, 0u);
+            sm.ts[o] = (int64_t)(((uint64_t)r[u].a.y << 32) | r[u].a.x);
+            sm.pod[o] = pc.x;
+            sm.cls[o] = pc.y;
+            sm.pid[o] = r[u].b.y;
+            sm.conn[o] = r[u].b.z;
+            sm.trsig[o] = r[u].b.w;
+            if (o >= live_beg && o < live_end) { cmin = min(cmin, pc.y); cmax = max(cmax, pc.y); }
+          }
+        }
+      } else if (count) {
         if (tid == 0) {
           mbar_expect_tx(&sm.bar, count * 24u);
           bulk_g2s(sm.ts, p.ev.ts + A, count * 8u, &sm.bar);
@@ -526,15 +597,10 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           bulk_g2s(sm.pid, p.ev.pid + A, count * 4u, &sm.bar);
           bulk_g2s(sm.conn, p.ev.conn + A, count * 4u, &sm.bar);
         }
-      }
-      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
-      const uint32_t live_beg = sm.rng[i0].x - A, live_end = min(count, sm.rng[i1 - 1].y - A);
-      if (count) {
         mbar_wait(&sm.bar, phase);
         phase ^= 1;
         // identity row -> (pod, class), once per staged event instead of once per (span, event) pair; and whether
         // the events the chunk's spans can reach all carry one class (then tier 4 is counted, not enumerated)
-        uint32_t cmin = 0xffffffffu, cmax = 0u;
         for (uint32_t o = tid; o < count; o += JT_THREADS) {
           const uint32_t row = sm.pod[o];
           const uint2 pc = row < p.n_idents ? __ldg(p.ident_pc + row) : make_uint2(0u, 0u);   // padding past the last event
@@ -542,6 +608,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           sm.cls[o] = pc.y;
           if (o >= live_beg && o < live_end) { cmin = min(cmin, pc.y); cmax = max(cmax, pc.y); }
         }
+      }
+      if (count) {
         cmin = __reduce_min_sync(0xffffffffu, cmin);
         cmax = __reduce_max_sync(0xffffffffu, cmax);
         if (lane == 0 && cmin <= cmax) { atomicMin(&sm.cls_min, cmin); atomicMax(&sm.cls_max, cmax); }
@@ -714,7 +782,9 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             const bool mine = r < p.fanout && top.idx[r] != 0xffffffffu;
             const uint32_t pos = __shfl_sync(pair, mine ? top.pos[r] : 0xffffffffu, lane & 30u);   // the even lane's final list
             const bool has = pos != 0xffffffffu;
-            vals[r] = has ? p.ev.val[pos] : 0.0;
+            // the candidate's value: from the sorted column, or from its input record when there is no sorted copy
+            const uint32_t in_idx = __shfl_sync(pair, top.idx[r], lane & 30u);
+            vals[r] = !has ? 0.0 : FUSED ? p.events_in[in_idx].value : p.ev.val[pos];
             sigs[r] = has ? (sm.trsig[pos - A] & 15u) : 0xffu;
             kept += has;
             present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
@@ -794,6 +864,7 @@ __global__ void k_list_all_spans(uint32_t *__restrict__ big_list, unsigned int *
 }
 
 // ---- spans whose own range exceeds a tile: one warp per span, straight from global memory ---------------
+template <bool FUSED>
 __global__ void __launch_bounds__(JT_THREADS)
 k_join_big(const __grid_constant__ JoinParams p, const uint32_t *__restrict__ big_list, const unsigned int *__restrict__ big_count) {
   __shared__ Cand s_list[JT_WARPS][JT_LIST];
@@ -803,12 +874,14 @@ k_join_big(const __grid_constant__ JoinParams p, const uint32_t *__restrict__ bi
   __syncthreads();
   unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
   const unsigned n = *big_count;
-  const Cols g{p.ev.ts, p.ev.ident, p.ev.pid, p.ev.conn, p.ev.trsig, p.ev_perm, 0u};
+  const ColsSorted gs{p.ev.ts, p.ev.val, p.ev.ident, p.ev.pid, p.ev.conn, p.ev.trsig, p.ev_perm};
+  const ColsIndirect gi{p.events_in, p.ev_perm};
   for (unsigned i = blockIdx.x * JT_WARPS + warp; i < n; i += gridDim.x * JT_WARPS) {
     const size_t q = big_list[i];
     const size_t si = p.span_perm ? p.span_perm[q] : q;
     const SpanRec s = load_span(p.spans + si);
-    process_span(p, g, s_list[warp], s, si, p.ranges[q], lane, w_matched, w_low, w_drop, w_cand, w_kept);
+    if (FUSED) process_span(p, gi, s_list[warp], s, si, p.ranges[q], lane, w_matched, w_low, w_drop, w_cand, w_kept);
+    else process_span(p, gs, s_list[warp], s, si, p.ranges[q], lane, w_matched, w_low, w_drop, w_cand, w_kept);
   }
   if (lane == 0) {
     if (w_matched) atomicAdd(&s_cnt[0], w_matched);
@@ -910,7 +983,7 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   }
   JoinParams p;
   p.spans = a.spans; p.span_perm = a.span_perm; p.n_spans = a.n_spans;
-  p.ev = a.ev.col; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv; p.ranges2 = ranges2;
+  p.ev = a.ev.col; p.events_in = a.events_in; p.ev_perm = a.ev.perm; p.ranges = (const uint4 *)rv; p.ranges2 = ranges2;
   p.idents = a.idents; p.n_idents = (uint32_t)a.n_idents;
   p.ident_pc = a.ident_pc;
   if (!p.ident_pc) LSG_TRY(lsg_ident_classes(ctx, a.idents, a.n_idents, &p.ident_pc));
@@ -939,10 +1012,15 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   // inner ranges reach at most min(W, 500 ms) + two time quanta from the span: 32-bit deltas when that is < 2^31 ns
   const int64_t wi = a.window_ns < 500 * kMs ? a.window_ns : 500 * kMs;
   const bool t32 = a.ev.key.shift < 29 && wi + ((int64_t)2 << a.ev.key.shift) < ((int64_t)1 << 31);
+  // no sorted copy of the events (lsg_sort_events_finish was told not to gather): the kernels read through the permutation
+  const bool fused = a.ev.col.ts == nullptr;
+  if (fused && !a.events_in) return lsg_fail(ctx, LSG_ERR_INVALID, "join without sorted columns needs the input records");
   if (a.fanout <= 3) {
-    if (t32) LSG_TRY(launch(k_join_tiles<3, true>)); else LSG_TRY(launch(k_join_tiles<3, false>));
+    if (fused) { if (t32) LSG_TRY(launch(k_join_tiles<3, true, true>)); else LSG_TRY(launch(k_join_tiles<3, false, true>)); }
+    else { if (t32) LSG_TRY(launch(k_join_tiles<3, true, false>)); else LSG_TRY(launch(k_join_tiles<3, false, false>)); }
   } else if (a.fanout <= TM_MAX_F) {
-    if (t32) LSG_TRY(launch(k_join_tiles<TM_MAX_F, true>)); else LSG_TRY(launch(k_join_tiles<TM_MAX_F, false>));
+    if (fused) { if (t32) LSG_TRY(launch(k_join_tiles<TM_MAX_F, true, true>)); else LSG_TRY(launch(k_join_tiles<TM_MAX_F, false, true>)); }
+    else { if (t32) LSG_TRY(launch(k_join_tiles<TM_MAX_F, true, false>)); else LSG_TRY(launch(k_join_tiles<TM_MAX_F, false, false>)); }
   } else {
     // more kept candidates than the tile kernel holds in registers: every span goes to the warp-per-span kernel
     k_list_all_spans<<<(unsigned)std::min<size_t>((a.n_spans + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
@@ -952,7 +1030,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   {
     size_t blocks = (a.n_spans + JT_WARPS - 1) / JT_WARPS, cap = (size_t)ctx->sm_count * 4;
     if (blocks > cap) blocks = cap;
-    k_join_big<<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
+    if (fused) k_join_big<true><<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
+    else k_join_big<false><<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
   }
   LSG_LAUNCH_CHECK(ctx);
   return 0;

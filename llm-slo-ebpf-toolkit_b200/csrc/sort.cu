@@ -669,7 +669,7 @@ int bits_of(uint64_t v) {
 int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                     int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out, nullptr, 0));
-  return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out, !exact);
+  return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out, !exact, true);
 }
 
 // phase 1: one pass over the events for the key layout (time range, group count) and the analytic counters
@@ -751,14 +751,14 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
 // phase 2: place the events.  Counting sort when the key space is small (and the caller does not need a stable,
 // exact order), else keys + radix passes + gather.
 int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting) {
+                           lsg_event *sorted_out, SortedEvents *out, bool allow_counting, bool want_copy) {
   const KeySpec ks = out->key;
   if (n == 0) return 0;
   EventStats *tally_dst = out->tally_in_sort ? const_cast<EventStats *>(out->stats_dev) : nullptr;
   // where the events go: the caller's record array, or columns in the workspace (padded so that a 16-byte aligned
   // bulk copy may run a little past the last event)
   int64_t *c_ts = nullptr; double *c_val = nullptr; uint32_t *c_ident = nullptr, *c_pid = nullptr, *c_conn = nullptr, *c_trsig = nullptr;
-  if (!sorted_out) {
+  if (!sorted_out && want_copy) {
     const size_t n_pad = ((n + 3) & ~(size_t)3) + 4;
     void *sv;
     LSG_TRY(lsg_ws(ctx, WS_EV_SORTED, n_pad * 32, &sv));
@@ -772,6 +772,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
     out->rec = sorted_out;
   }
   auto gather = [&](const uint32_t *perm, size_t count, const uint32_t *n_placed) -> int {
+    if (!sorted_out && !want_copy) return 0;   // the consumer reads the input records through the permutation
     ProfScope ps(ctx, PK_GATHER);
     if (sorted_out) k_gather_events<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, n_placed, sorted_out);
     else k_gather_events_soa<<<grid_for(ctx, count, 256, 8), 256, 0, ctx->stream>>>(events, perm, count, n_placed, c_ts, c_val, c_ident, c_pid, c_conn, c_trsig);
