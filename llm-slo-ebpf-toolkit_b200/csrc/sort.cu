@@ -9,8 +9,12 @@
 // contiguous range, so the time quantum 2^shift is as large as the window allows (<= window/32) and the
 // key shrinks from ~50 bits to 23-30.  `exact` (lsg_sort_events_dev) uses shift 0.
 //
-// Two ways to group, both ending in ONE gather that moves the 32-byte records (random reads, sequential
-// writes; random 32-byte writes measured 2.6x slower):
+// The time axis of the key comes from the spans (first live span - window .. last live span + window: an event
+// outside it can match nothing), so nothing reads the events before the sort's own first pass.
+//
+// Two ways to group, both ending in a permutation (sorted position -> input index).  The pipeline stops there: the
+// join gathers its tiles through the permutation.  A gather that moves the 32-byte records (random reads, sequential
+// writes; random 32-byte writes measured 2.6x slower) only runs for lsg_sort_events_dev and with LSG_JOIN_SORTED_COPY:
 //   counting sort  (key space <= 2^25, not exact)  one counter per key in an L2-resident table:
 //                  k_count_keys (key + rank by returning atomic) -> exclusive scan -> k_place_events
 //                  (permutation).  Order inside one key = whatever the atomics gave.
@@ -428,7 +432,7 @@ k_gather_events_soa(const lsg_event *__restrict__ events, const uint32_t *__rest
 // ---- counting sort (small key spaces) --------------------------------------------------------------------------
 // With the coarse time quantum the whole key space of a batch is a few million values: one counter per key fits
 // in L2, so "sort" is: count the keys (L2 atomics), exclusive scan, place every record at a cursor fetch-add.
-// Three light passes instead of keys + 3 x (histogram, scan, scatter) + gather, and a span's event range becomes
+// Three light passes instead of keys + 3 x (histogram, scan, scatter), and a span's event range becomes
 // two table reads.  The order of the events inside one key is whatever the atomics give: the join does not care
 // (it selects by an explicit total order), and lsg_sort_events_dev never takes this path.
 constexpr uint32_t COUNTING_MAX_KEYS = 1u << 25;   // 128 MB of counters at most
@@ -474,8 +478,8 @@ k_count_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
 
 // pass 3 (after the scan turned the counts into run starts): position = start of the key's run + rank.
 // Only the permutation is scattered (4-byte writes into an array that stays in L2); the 32-byte records are moved
-// afterwards by the gather: random READS of records are cheap, random 32-byte WRITES into a 320 MB output are not
-// (measured: 0.74 ms for 10 M records against 0.28 ms for the gather).
+// by whoever needs them (the join's tile loader, or the gather): random READS of records are cheap, random 32-byte
+// WRITES into a 320 MB output are not (measured: 0.74 ms for 10 M records against 0.25 ms for a gather).
 __global__ void __launch_bounds__(256)
 k_place_events(const uint2 *__restrict__ key_rank, size_t n, const uint32_t *__restrict__ bins, uint32_t *__restrict__ perm) {
   // two dependent random accesses per event (run start, then the permutation slot): four events per thread in flight
