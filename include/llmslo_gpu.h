@@ -125,7 +125,7 @@ typedef struct {
 } lsg_confusion_out;
 
 /* per (incident, signal) features of the A7 glue.  Only `max` has a reference counterpart
- * (correlator.go:109-111); count/sum/sketch are defined by this library (oracle/oracle.h). */
+ * (correlator.go:109-111); count/sum/sketch are defined by this library (and restated for the tests in oracle/oracle.cpp). */
 #define LSG_SKETCH_BINS 16
 typedef struct {
   uint32_t count;                    /* spans of the incident that carry the signal        */
