@@ -289,6 +289,12 @@ typedef struct {
   uint32_t *cand_event; uint8_t *cand_tier; double *attr_out; double *conf_out;
   double *inc_signals; double *posterior; uint8_t *top1;
   uint64_t *counters_dev;
+  /* compact form of the per-span attributes (optional, NULL = not wanted): the kept candidates' signal index
+   * (0..11, 0xff = empty slot) and value, [n_spans * fanout] each, in cand_event's order.  Without base attributes a
+   * span's enriched attributes are exactly max(value) per signal over these (correlator.go:106-112) and its
+   * confidence is the first candidate's tier confidence (correlator.go:113-118), so a caller that takes these may
+   * pass attr_out = conf_out = NULL and move 42 instead of 119 bytes per span back to the host. */
+  double *cand_value; uint8_t *cand_sig;
 } lsg_pipeline_args;
 /* asynchronous: returns after enqueueing on the context's stream (it synchronises once inside, after the
  * first reduction, to read the key layout back) */

@@ -76,7 +76,7 @@ class PipelineArgs(C.Structure):
                 ("window_ns", C.c_int64), ("threshold", C.c_double), ("fanout", C.c_int), ("coverage_thr", C.c_double),
                 ("cand_event", C.c_void_p), ("cand_tier", C.c_void_p), ("attr_out", C.c_void_p),
                 ("conf_out", C.c_void_p), ("inc_signals", C.c_void_p), ("posterior", C.c_void_p),
-                ("top1", C.c_void_p), ("counters_dev", C.c_void_p)]
+                ("top1", C.c_void_p), ("counters_dev", C.c_void_p), ("cand_value", C.c_void_p), ("cand_sig", C.c_void_p)]
 
 
 class SynthCfg(C.Structure):

@@ -114,7 +114,8 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        const lsg_ident *idents, size_t n_idents, int64_t window_ns, double threshold, int fanout,
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
                        double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
-                       unsigned long long *inc_keys = nullptr, size_t n_incidents = 0) {
+                       unsigned long long *inc_keys = nullptr, size_t n_incidents = 0, double *cand_value = nullptr,
+                       uint8_t *cand_sig = nullptr) {
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans));
   // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
@@ -146,6 +147,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   ja.counters = (uint64_t *)((char *)small_v + SMALL_JOIN);
   ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
   ja.ident_pc = ident_pc;
+  ja.cand_value = cand_value; ja.cand_sig = cand_sig;
   LSG_TRY(lsg_launch_join(ctx, ja));
   *join_counters_dev = ja.counters;
   return 0;
@@ -584,7 +586,8 @@ int lsg_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted,
 // ---- the whole hot path, device resident ------------------------------------------------------------
 int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   if (!ctx || !a) return LSG_ERR_INVALID;
-  if (!a->spans || !a->events || !a->idents || !a->cand_event || !a->cand_tier || !a->attr_out || !a->conf_out ||
+  // attr_out, conf_out, cand_value and cand_sig are optional outputs
+  if (!a->spans || !a->events || !a->idents || !a->cand_event || !a->cand_tier ||
       !a->inc_signals || !a->posterior || !a->top1 || !a->counters_dev || !a->inc_actual || !a->inc_expected ||
       !a->inc_expected_n)
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
@@ -602,7 +605,7 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   LSG_CUDA(ctx, cudaMemsetAsync(acc, 0, a->n_incidents * LSG_NSIG * 8, ctx->stream));
   LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, a->events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
                              fanout, nullptr, a->cand_event, a->cand_tier, a->attr_out, a->conf_out, nullptr, nullptr, &jc_dev,
-                             &sorted, (unsigned long long *)acc, a->n_incidents));
+                             &sorted, (unsigned long long *)acc, a->n_incidents, a->cand_value, a->cand_sig));
   LSG_TRY(lsg_launch_incident_finish(ctx, (const unsigned long long *)acc, a->n_incidents, a->inc_signals));
   LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
   LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
@@ -630,8 +633,10 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   LSG_TRY(h2d(ctx, WS_IN2, a->inc_expected_n, a->n_incidents, &d.inc_expected_n));
   LSG_TRY(dalloc(ctx, WS_OUT0, true, a->n_spans * f, &d.cand_event));
   LSG_TRY(dalloc(ctx, WS_OUT1, true, a->n_spans * f, &d.cand_tier));
-  LSG_TRY(dalloc(ctx, WS_OUT2, true, a->n_spans * LSG_NSIG, &d.attr_out));
-  LSG_TRY(dalloc(ctx, WS_OUT3, true, a->n_spans, &d.conf_out));
+  LSG_TRY(dalloc(ctx, WS_OUT2, a->attr_out != nullptr, a->n_spans * LSG_NSIG, &d.attr_out));   // only what the caller takes
+  LSG_TRY(dalloc(ctx, WS_OUT3, a->conf_out != nullptr, a->n_spans, &d.conf_out));
+  LSG_TRY(dalloc(ctx, WS_OUT6, a->cand_value != nullptr, a->n_spans * f, &d.cand_value));
+  LSG_TRY(dalloc(ctx, WS_OUT7, a->cand_sig != nullptr, a->n_spans * f, &d.cand_sig));
   LSG_TRY(dalloc(ctx, WS_OUT4, true, a->n_incidents * LSG_NSIG, &d.inc_signals));
   LSG_TRY(dalloc(ctx, WS_OUT5, true, a->n_incidents * LSG_NDOM, &d.posterior));
   LSG_TRY(dalloc(ctx, WS_IN3, true, a->n_incidents, &d.top1));
@@ -641,6 +646,8 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   LSG_TRY(d2h(ctx, a->cand_tier, (const uint8_t *)d.cand_tier, a->n_spans * f));
   LSG_TRY(d2h(ctx, a->attr_out, (const double *)d.attr_out, a->n_spans * LSG_NSIG));
   LSG_TRY(d2h(ctx, a->conf_out, (const double *)d.conf_out, a->n_spans));
+  LSG_TRY(d2h(ctx, a->cand_value, (const double *)d.cand_value, a->n_spans * f));
+  LSG_TRY(d2h(ctx, a->cand_sig, (const uint8_t *)d.cand_sig, a->n_spans * f));
   LSG_TRY(d2h(ctx, a->inc_signals, (const double *)d.inc_signals, a->n_incidents * LSG_NSIG));
   LSG_TRY(d2h(ctx, a->posterior, (const double *)d.posterior, a->n_incidents * LSG_NDOM));
   LSG_TRY(d2h(ctx, a->top1, (const uint8_t *)d.top1, a->n_incidents));
@@ -662,8 +669,8 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
 // must stay untouched between submit and wait, and should be pinned (otherwise the copies serialise).
 }  // extern "C"
 namespace {
-enum { PB_EVENTS = 0, PB_SPANS, PB_IDENTS, PB_ACT, PB_EXP, PB_EXPN, PB_CE, PB_CT, PB_ATTR, PB_CONF, PB_SIG, PB_POST, PB_TOP1, PB_CNT, PB_BUFS };
-static_assert(PB_BUFS == 14, "WS_PIPE reserves 14 buffers per slot");
+enum { PB_EVENTS = 0, PB_SPANS, PB_IDENTS, PB_ACT, PB_EXP, PB_EXPN, PB_CE, PB_CT, PB_ATTR, PB_CONF, PB_SIG, PB_POST, PB_TOP1, PB_CNT, PB_CV, PB_CS, PB_BUFS };
+static_assert(PB_BUFS == 16, "WS_PIPE reserves 16 buffers per slot");
 
 int pipe_init(lsg_ctx *ctx) {
   if (ctx->up) return 0;
@@ -705,8 +712,11 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   LSG_TRY(pipe_buf(ctx, slot, PB_EXPN, a->n_incidents, &d_expn));
   LSG_TRY(pipe_buf(ctx, slot, PB_CE, a->n_spans * f, &d.cand_event));
   LSG_TRY(pipe_buf(ctx, slot, PB_CT, a->n_spans * f, &d.cand_tier));
-  LSG_TRY(pipe_buf(ctx, slot, PB_ATTR, a->n_spans * LSG_NSIG, &d.attr_out));
-  LSG_TRY(pipe_buf(ctx, slot, PB_CONF, a->n_spans, &d.conf_out));
+  d.attr_out = nullptr; d.conf_out = nullptr; d.cand_value = nullptr; d.cand_sig = nullptr;   // only what the caller takes
+  if (a->attr_out) LSG_TRY(pipe_buf(ctx, slot, PB_ATTR, a->n_spans * LSG_NSIG, &d.attr_out));
+  if (a->conf_out) LSG_TRY(pipe_buf(ctx, slot, PB_CONF, a->n_spans, &d.conf_out));
+  if (a->cand_value) LSG_TRY(pipe_buf(ctx, slot, PB_CV, a->n_spans * f, &d.cand_value));
+  if (a->cand_sig) LSG_TRY(pipe_buf(ctx, slot, PB_CS, a->n_spans * f, &d.cand_sig));
   LSG_TRY(pipe_buf(ctx, slot, PB_SIG, a->n_incidents * LSG_NSIG, &d.inc_signals));
   LSG_TRY(pipe_buf(ctx, slot, PB_POST, a->n_incidents * LSG_NDOM, &d.posterior));
   LSG_TRY(pipe_buf(ctx, slot, PB_TOP1, a->n_incidents, &d.top1));
@@ -738,6 +748,8 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   LSG_TRY(down(a->cand_tier, d.cand_tier, a->n_spans * f));
   LSG_TRY(down(a->attr_out, d.attr_out, a->n_spans * LSG_NSIG * 8));
   LSG_TRY(down(a->conf_out, d.conf_out, a->n_spans * 8));
+  LSG_TRY(down(a->cand_value, d.cand_value, a->n_spans * f * 8));
+  LSG_TRY(down(a->cand_sig, d.cand_sig, a->n_spans * f));
   LSG_TRY(down(a->inc_signals, d.inc_signals, a->n_incidents * LSG_NSIG * 8));
   LSG_TRY(down(a->posterior, d.posterior, a->n_incidents * LSG_NDOM * 8));
   LSG_TRY(down(a->top1, d.top1, a->n_incidents));

@@ -33,6 +33,8 @@ enum {
   WS_OUT3,
   WS_OUT4,
   WS_OUT5,
+  WS_OUT6,
+  WS_OUT7,
   WS_IN0,            // host-API staging of misc inputs
   WS_IN1,
   WS_IN2,
@@ -46,7 +48,7 @@ enum {
   WS_IDENT_PC,       // join: (pod, service+node class) per identity row
   WS_IDENT_TABLE,    // join: hash table that numbers the (service, node) classes
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
-  WS_PIPE_END = WS_PIPE + 2 * 14 - 1,
+  WS_PIPE_END = WS_PIPE + 2 * 16 - 1,
   WS_COUNT
 };
 
@@ -306,6 +308,7 @@ struct JoinArgs {
   // optional fusion of the A7 glue: per (incident, signal) max keys updated straight from the join's epilogue
   unsigned long long *inc_keys; size_t n_incidents;
   const uint2 *ident_pc;   // lsg_ident_classes() of `idents`, or NULL: lsg_launch_join computes it
+  double *cand_value; uint8_t *cand_sig;   // optional: value and signal of every kept candidate, [n_spans * fanout]
 };
 int lsg_launch_join(lsg_ctx *, const JoinArgs &);
 // per identity row: x = pod id, y = class of its (service, node) pair (0 when either is empty; equal pairs get

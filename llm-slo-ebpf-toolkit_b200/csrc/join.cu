@@ -60,8 +60,10 @@ struct JoinParams {
   const double *attr_base;
   uint32_t *cand_event;
   uint8_t *cand_tier;
-  double *attr_out;
-  double *conf_out;
+  double *attr_out;          // may be NULL (not wanted)
+  double *conf_out;          // may be NULL
+  double *cand_value;        // optional compact form: value and signal of the kept candidates, [n_spans * fanout]
+  uint8_t *cand_sig;
   double *retrieval_out;
   uint32_t *n_cand_out;
   unsigned long long *counters;  // [0] matched [1] low_confidence [2] fanout_dropped [3] candidates [4] kept [5] bad ident
@@ -377,20 +379,24 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
     my_val = c.val(my_pos);
     my_sig = c.trsig(my_pos) & 15u;
   }
+  if ((int)lane < p.fanout) {
+    if (p.cand_value) p.cand_value[si * (size_t)p.fanout + lane] = my_val;
+    if (p.cand_sig) p.cand_sig[si * (size_t)p.fanout + lane] = (uint8_t)my_sig;
+  }
   for (int r = 0; r < kept; ++r) {
     const double v = __shfl_sync(0xffffffffu, my_val, r);
     const unsigned sig = __shfl_sync(0xffffffffu, my_sig, r);
     if (sig == lane && (isnan(val) || v > val)) val = v;
   }
   if (lane < LSG_NSIG) {
-    p.attr_out[si * LSG_NSIG + lane] = val;
+    if (p.attr_out) p.attr_out[si * LSG_NSIG + lane] = val;
     if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(val))
       atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + lane], f64_key(val));   // A7 glue: max per incident and signal
   }
   // llm.ebpf.correlation_confidence = max confidence = the first kept candidate's (correlator.go:113-118)
   const double v3 = __shfl_sync(0xffffffffu, val, 3), v4 = __shfl_sync(0xffffffffu, val, 4);
   if (lane == 0) {
-    p.conf_out[si] = kept ? lsg_tier_conf((int)first_tier) : 0.0;
+    if (p.conf_out) p.conf_out[si] = kept ? lsg_tier_conf((int)first_tier) : 0.0;
     if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
       double total = 0.0;
       if (!isnan(val)) total += val;
@@ -791,6 +797,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             if (!h && r < p.fanout) {
               p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
               p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
+              if (p.cand_value) p.cand_value[si * (size_t)p.fanout + r] = vals[r];
+              if (p.cand_sig) p.cand_sig[si * (size_t)p.fanout + r] = (uint8_t)sigs[r];
             }
           }
           // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
@@ -805,7 +813,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
               for (int r = 0; r < F; ++r)
                 if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
             }
-            p.attr_out[si * LSG_NSIG + col] = v;
+            if (p.attr_out) p.attr_out[si * LSG_NSIG + col] = v;
             if (to_incident && !isnan(v))
               atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
             if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
@@ -817,7 +825,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             n_match += n_tr;
             if (cut < 1) n_low += n_tr;
             // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
-            p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
+            if (p.conf_out) p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
             if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
               double total = 0.0;
               if (!isnan(v0)) total += v0;
@@ -990,6 +998,7 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   p.window_ns = a.window_ns; p.threshold = a.threshold; p.fanout = a.fanout;
   p.attr_base = a.attr_base; p.cand_event = a.cand_event; p.cand_tier = a.cand_tier; p.attr_out = a.attr_out;
   p.conf_out = a.conf_out; p.retrieval_out = a.retrieval_out; p.n_cand_out = a.n_cand_out;
+  p.cand_value = a.cand_value; p.cand_sig = a.cand_sig;
   p.counters = (unsigned long long *)a.counters;
   p.inc_keys = a.inc_keys; p.n_incidents = a.n_incidents;
   const size_t n_chunks = (a.n_spans + JT_CH - 1) / JT_CH;

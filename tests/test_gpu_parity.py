@@ -487,3 +487,53 @@ def test_host_pipeline_blocking_and_double_buffered(ctx):
     c = A.Counters()
     ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(c))
     check(c, outs, batches[1])
+
+
+def test_compact_span_outputs_rebuild_the_dense_ones(ctx):
+    """lsg_pipeline_args.cand_value / cand_sig: the kept candidates' value and signal are enough to rebuild a span's
+    attribute row (max per signal, correlator.go:106-112) and confidence (first candidate's tier, correlator.go:113-118),
+    so a host caller may leave attr_out / conf_out NULL and download a third of the bytes."""
+    for fanout, ne, ns, horizon in ((3, 200_000, 20_000, 60), (8, 60_000, 6_000, 10), (12, 30_000, 300, 1)):
+        cfg = synth.config(ne, ns, 16, 8, 2, seed=40 + fanout, horizon_ns=horizon * 1_000_000_000)
+        w = synth.generate_host(cfg)
+        n_s, n_i = len(w["spans"]), len(w["inc_actual"])
+        keep = {k: np.ascontiguousarray(w[k]) for k in ("spans", "events", "idents", "inc_actual", "inc_expected", "inc_expected_n")}
+
+        def run(dense, compact):
+            o = {"ce": np.zeros(n_s * fanout, np.uint32), "ct": np.zeros(n_s * fanout, np.uint8),
+                 "attr": np.zeros(n_s * A.NSIG), "conf": np.zeros(n_s), "sig": np.zeros(n_i * A.NSIG),
+                 "post": np.zeros(n_i * A.NDOM), "top1": np.zeros(n_i, np.uint8),
+                 "cv": np.full(n_s * fanout, -1.0), "cs": np.full(n_s * fanout, 7, np.uint8)}
+            args = A.PipelineArgs(keep["spans"].ctypes.data, n_s, keep["events"].ctypes.data, len(w["events"]),
+                                  keep["idents"].ctypes.data, len(w["idents"]), n_i, keep["inc_actual"].ctypes.data,
+                                  keep["inc_expected"].ctypes.data, keep["inc_expected_n"].ctypes.data, 0, 0.0, fanout, 0.10,
+                                  o["ce"].ctypes.data, o["ct"].ctypes.data, o["attr"].ctypes.data if dense else None,
+                                  o["conf"].ctypes.data if dense else None, o["sig"].ctypes.data, o["post"].ctypes.data,
+                                  o["top1"].ctypes.data, None, o["cv"].ctypes.data if compact else None,
+                                  o["cs"].ctypes.data if compact else None)
+            c = A.Counters()
+            ctx.call_dev("lsg_pipeline", C.byref(args), C.byref(c))
+            return o, c
+
+        dense, c_dense = run(True, False)
+        both, c_both = run(True, True)
+        comp, c_comp = run(False, True)
+        assert bytes(c_dense) == bytes(c_both) == bytes(c_comp)
+        for k in ("ce", "ct", "sig", "post", "top1"):
+            assert np.array_equal(dense[k], comp[k], equal_nan=True) and np.array_equal(dense[k], both[k], equal_nan=True), k
+        assert np.array_equal(both["cv"], comp["cv"]) and np.array_equal(both["cs"], comp["cs"])
+        assert not comp["attr"].any() and not comp["conf"].any()          # not requested: left untouched
+        ce, ct = comp["ce"].reshape(n_s, fanout), comp["ct"].reshape(n_s, fanout)
+        cv, cs = comp["cv"].reshape(n_s, fanout), comp["cs"].reshape(n_s, fanout)
+        has = ce != A.NONE
+        assert ((cs == 0xFF) == ~has).all() and (cv[~has] == 0).all()
+        assert np.array_equal(cs[has], (w["events"]["trace_sig"][ce[has]] & 15).astype(np.uint8))
+        assert np.array_equal(cv[has], w["events"]["value"][ce[has]])
+        attr = np.full((n_s, A.NSIG), np.nan)
+        for r in range(fanout):                                            # max per signal over the kept candidates
+            rows = np.nonzero(has[:, r])[0]
+            cur = attr[rows, cs[rows, r]]
+            attr[rows, cs[rows, r]] = np.where(np.isnan(cur) | (cv[rows, r] > cur), cv[rows, r], cur)
+        assert np.array_equal(attr.reshape(-1), dense["attr"], equal_nan=True)
+        conf = np.where(has[:, 0], np.array(A.TIER_CONF)[ct[:, 0]], 0.0)
+        assert np.array_equal(conf, dense["conf"])
