@@ -545,6 +545,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     while (i0 < nq) {
       const uint32_t A = sm.rng[i0].x & ~3u;   // 16-byte aligned start for every column
       if (tid == 0) { sm.cls_min = 0xffffffffu; sm.cls_max = 0u; }   // published by the barrier below
+      if (FUSED && (int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }   // the loader already notes
       // spans of the chunk whose outer range still ends inside a tile that starts at A (ranges are monotone)
       const bool fits = (int)tid >= i0 && (int)tid < nq && sm.rng[tid].y - A <= (uint32_t)(TM_CAP - 4);
       const int n_fit = __syncthreads_count(fits);
@@ -557,9 +558,31 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       const int i1 = i0 + n_fit;
       const uint32_t Bend = (sm.rng[i1 - 1].y + 3u) & ~3u;
       const uint32_t count = Bend > A ? Bend - A : 0;   // <= TM_CAP, multiple of 4; the columns are padded past n
-      if ((int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
+      if (!FUSED && (int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
       const uint32_t live_beg = sm.rng[i0].x - A, live_end = min(count, sm.rng[i1 - 1].y - A);
       uint32_t cmin = 0xffffffffu, cmax = 0u;
+      // tier 1 for one tile event: probe the hash of the chunk's span trace ids, note the spans it falls into
+      auto probe_trace = [&](const uint32_t o, const uint32_t tr, const int64_t e_ts) {
+        if (tr == 0) return;
+        uint32_t slot = trace_slot(tr);
+        uint32_t key;
+        while ((key = sm.hkey[slot]) != 0u && key != tr) slot = (slot + 1) & (TM_HASH - 1);
+        if (key != tr) return;
+        for (uint32_t k = sm.hhead[slot]; k != TM_END; k = sm.hnext[k]) {
+          if ((int)k < i0 || (int)k >= i1) continue;                 // that span belongs to another tile of the chunk
+          const uint4 rg = sm.rng[k];
+          if (o + A < rg.x || o + A >= rg.y) continue;                // outside its range: cannot be within the window
+          const int64_t s_ts = (int64_t)(((uint64_t)sm.span[k][0].y << 32) | sm.span[k][0].x);
+          const uint64_t adt = lsg_absdiff(s_ts, e_ts);
+          if (adt > W) continue;                                      // outer window, dns.go:54-56
+          atomicAdd(&sm.n_tr[k], 1u);
+          if (adt <= Wi) atomicAdd(&sm.n_tr_in[k], 1u);
+          if (cut >= 1) {
+            const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
+            if (at < TM_LIST) sm.note[at][k] = (uint16_t)((LSG_TIER_TRACE << 12) | o);
+          }
+        }
+      };
       if (FUSED) {
         // every thread gathers its share of the tile (at most TM_CAP / JT_THREADS = 7 records): first all its
         // permutation entries (coalesced), then the records four at a time as independent 256-bit loads
@@ -592,6 +615,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             sm.conn[o] = r[u].b.z;
             sm.trsig[o] = r[u].b.w;
             if (o >= live_beg && o < live_end) { cmin = min(cmin, pc.y); cmax = max(cmax, pc.y); }
+            // tier 1 while the record is still in registers: no second pass over the tile, one barrier less
+            if (o < live_end) probe_trace(o, r[u].b.w >> 4, (int64_t)(((uint64_t)r[u].a.y << 32) | r[u].a.x));
           }
         }
       } else if (count) {
@@ -621,30 +646,11 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         if (lane == 0 && cmin <= cmax) { atomicMin(&sm.cls_min, cmin); atomicMax(&sm.cls_max, cmax); }
       }
       __syncthreads();
-      // ---- tier 1: every event of the tile probes the hash once
-      for (uint32_t o = tid; o < live_end; o += JT_THREADS) {
-        const uint32_t tr = sm.trsig[o] >> 4;
-        if (tr == 0) continue;
-        uint32_t slot = trace_slot(tr);
-        uint32_t key;
-        while ((key = sm.hkey[slot]) != 0u && key != tr) slot = (slot + 1) & (TM_HASH - 1);
-        if (key != tr) continue;
-        const int64_t e_ts = sm.ts[o];
-        for (uint32_t k = sm.hhead[slot]; k != TM_END; k = sm.hnext[k]) {
-          if ((int)k < i0 || (int)k >= i1) continue;                 // that span belongs to another tile of the chunk
-          const uint4 rg = sm.rng[k];
-          if (o + A < rg.x || o + A >= rg.y) continue;                // outside its range: cannot be within the window
-          const int64_t s_ts = (int64_t)(((uint64_t)sm.span[k][0].y << 32) | sm.span[k][0].x);
-          if (lsg_absdiff(s_ts, e_ts) > W) continue;                  // outer window, dns.go:54-56
-          atomicAdd(&sm.n_tr[k], 1u);
-          if (lsg_absdiff(s_ts, e_ts) <= Wi) atomicAdd(&sm.n_tr_in[k], 1u);
-          if (cut >= 1) {
-            const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-            if (at < TM_LIST) sm.note[at][k] = (uint16_t)((LSG_TIER_TRACE << 12) | o);
-          }
-        }
+      // ---- tier 1 (unfused): every event of the tile probes the hash once
+      if (!FUSED) {
+        for (uint32_t o = tid; o < live_end; o += JT_THREADS) probe_trace(o, sm.trsig[o] >> 4, sm.ts[o]);
+        __syncthreads();   // the hash pass (short, evenly spread) is complete: from here on a span only needs its own two lanes
       }
-      __syncthreads();   // the hash pass (short, evenly spread) is complete: from here on a span only needs its own two lanes
       // ---- tiers 2-4: thread (2k + h) walks half h of span k's inner range
       const bool uniform = sm.cls_min == sm.cls_max;
       const int k = i0 + (int)(tid >> 1);
