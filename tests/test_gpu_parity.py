@@ -537,3 +537,31 @@ def test_compact_span_outputs_rebuild_the_dense_ones(ctx):
         assert np.array_equal(attr.reshape(-1), dense["attr"], equal_nan=True)
         conf = np.where(has[:, 0], np.array(A.TIER_CONF)[ct[:, 0]], 0.0)
         assert np.array_equal(conf, dense["conf"])
+
+
+@pytest.mark.parametrize("case", range(24))
+def test_randomized_configs_vs_indexed_oracle(ctx, case):
+    """Seeded random draws of (sizes, pods, class shape, horizon, window, threshold, fanout): every special path of the
+    join (counted service+node tier, note-list overflow, spans beyond a tile, fanout above the register list, radix keys)
+    is reached by some of them; each must equal the indexed oracle field for field."""
+    rng = np.random.default_rng(1000 + case)
+    n_pods = int(rng.choice([2, 4, 8, 16, 64, 256]))
+    ppg = int(rng.choice([1, 2, 4]))
+    ppg = min(ppg, n_pods)
+    ppn = max(ppg, int(rng.choice([ppg, 2 * ppg, 4 * ppg])))
+    ppn = min(ppn, n_pods)
+    n_spans = int(rng.integers(200, 20_000))
+    n_events = int(n_spans * rng.choice([2, 5, 10, 20]))
+    horizon_s = float(rng.choice([0.5, 5, 60, 3600, 400 * 86400]))
+    window_ms = int(rng.choice([1, 40, 100, 249, 250, 251, 499, 500, 501, 2000, 10_000, 120_000]))
+    thr = float(rng.choice([0.5, 0.65, 0.66, 0.7, 0.8, 0.81, 0.9, 0.95, 1.0, 1.01]))
+    fanout = int(rng.choice([1, 2, 3, 4, 8, 9, 32]))
+    cfg = synth.config(n_events, n_spans, n_pods, ppn, ppg, seed=77 + case, horizon_ns=int(horizon_s * 1e9),
+                       multi_fault=case & 1)
+    w = synth.generate_host(cfg)
+    ids = w["idents"].copy()
+    if case % 5 == 4:
+        ids["service"][rng.integers(0, len(ids), max(1, len(ids) // 4))] = 0   # rows without a (service, node) class
+    got = ctx.process_batch(w["spans"], w["events"], ids, window_ms * 1_000_000, thr, fanout)
+    want = O.process_batch(w["spans"], w["events"], ids, window_ms * 1_000_000, thr, fanout, indexed=True, nthreads=8)
+    _eq_batch(got, want)
