@@ -10,7 +10,7 @@ Python loops: small cases only.  The packed-record C++ oracle (oracle/oracle.cpp
 this one through the interner (tests/test_oracle_packed.py) and is what the GPU is compared against
 at size.  Parity status: PINNED by pkg/correlation/testdata/labeled_pairs.jsonl (55 labelled pairs),
 pkg/attribution/testdata/multi_fault_samples.jsonl and the assertions of the reference's *_test.go
-files transcribed in tests/test_reference_vectors.py.
+files transcribed in tests/test_oracle_str.py (CPU) and tests/test_gpu_reference_vectors.py (the same vectors through the GPU).
 
 Every function cites the reference file:line it follows (paths relative to the reference root).
 """
