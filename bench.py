@@ -200,6 +200,8 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the host-buffer measurement (default min(steps, 10))")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-key-hint", action="store_true",
+                    help="do not state the spans' time range (lsg_pipeline_args.key_hint): the step then reads the key layout back")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer measurement (C3 needs 37 GB of pinned memory)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -236,6 +238,8 @@ def main():
 
     with torch.cuda.stream(stream):
         wl = DeviceWorkload(ctx, cfg)
+        if not args.no_key_hint:
+            wl.state_key_range()   # a replay knows its window: no readback of the key layout inside the step
 
         # The only exchange of the path is the sum of the counter block (N > 1).  Two blocks alternate, so the allreduce of
         # batch k (asynchronous, on NCCL's stream) overlaps the kernels of batch k + 1; it is waited for before its
@@ -479,7 +483,9 @@ def main():
             "config": {"workload": wl_name, "events_per_gpu": wl.n_events, "spans_per_gpu": wl.n_spans,
                        "incidents_per_gpu": wl.n_incidents, "window_ms": 2000, "threshold": 0.7, "fanout": 3,
                        "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((wl.n_events + wl.n_spans) * 32 / 1e6),
-                       "sort": dict(sort_info, method="counting" if counting else "radix"), "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
+                       "sort": dict(sort_info, method="counting" if counting else "radix"),
+                       "key_hint": "spans' time range and group count stated by the caller (checked on the device; --no-key-hint reads the key layout back instead)" if not args.no_key_hint else "none",
+                       "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
             "e2e": e2e,
             "gpu_launches": int(launches),
             "roofline": roofline,

@@ -270,8 +270,8 @@ typedef struct {
   lsg_debug debug;
   lsg_confusion_out confusion;
   uint64_t events, spans, incidents, candidates, kept;
-  uint64_t bad_idents; /* non-zero: some event's or span's ident was outside the identity table and the batch's results
-                          are void.  lsg_pipeline and lsg_pipeline_wait turn it into LSG_ERR_RANGE; a caller of
+  uint64_t bad_idents; /* non-zero: some event's or span's ident was outside the identity table (or the caller's key_hint
+                          did not hold) and the batch's results are void.  lsg_pipeline and lsg_pipeline_wait turn it into LSG_ERR_RANGE; a caller of
                           lsg_pipeline_dev checks it after reading the counters back (summed over ranks it stays non-zero) */
 } lsg_counters;
 #define LSG_COUNTER_WORDS (sizeof(lsg_counters) / 8)
@@ -295,9 +295,16 @@ typedef struct {
    * confidence is the first candidate's tier confidence (correlator.go:113-118), so a caller that takes these may
    * pass attr_out = conf_out = NULL and move 42 instead of 119 bytes per span back to the host. */
   double *cand_value; uint8_t *cand_sig;
+  /* optional statement about the batch (key_hint != 0): every span that can match (non-zero time, group != 0) has its
+   * time inside [span_ts_lo, span_ts_hi], and no identity row's group exceeds max_grp_hint.  A replay knows both.  The
+   * key layout then follows from the statement, nothing is read back and lsg_pipeline_dev never synchronises (it can
+   * be captured in a CUDA graph once the workspace is warm).  The statement is checked on the device; if it does not
+   * hold the batch's results are void and counters.bad_idents is non-zero. */
+  uint32_t key_hint, max_grp_hint;
+  int64_t span_ts_lo, span_ts_hi;
 } lsg_pipeline_args;
-/* asynchronous: returns after enqueueing on the context's stream (it synchronises once inside, after the
- * first reduction, to read the key layout back) */
+/* asynchronous: returns after enqueueing on the context's stream (without key_hint it synchronises once inside, after
+ * the first reduction, to read the key layout back) */
 int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *args);
 /* the same with HOST buffers in and out (every pointer of `args` is a host pointer; outputs may be NULL):
  * copies up, runs, copies back, synchronises.  What ProcessBatch + BuildAttributionsBayes +

@@ -76,7 +76,8 @@ class PipelineArgs(C.Structure):
                 ("window_ns", C.c_int64), ("threshold", C.c_double), ("fanout", C.c_int), ("coverage_thr", C.c_double),
                 ("cand_event", C.c_void_p), ("cand_tier", C.c_void_p), ("attr_out", C.c_void_p),
                 ("conf_out", C.c_void_p), ("inc_signals", C.c_void_p), ("posterior", C.c_void_p),
-                ("top1", C.c_void_p), ("counters_dev", C.c_void_p), ("cand_value", C.c_void_p), ("cand_sig", C.c_void_p)]
+                ("top1", C.c_void_p), ("counters_dev", C.c_void_p), ("cand_value", C.c_void_p), ("cand_sig", C.c_void_p),
+                ("key_hint", C.c_uint32), ("max_grp_hint", C.c_uint32), ("span_ts_lo", C.c_int64), ("span_ts_hi", C.c_int64)]
 
 
 class SynthCfg(C.Structure):

@@ -115,8 +115,8 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
                        double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
                        unsigned long long *inc_keys = nullptr, size_t n_incidents = 0, double *cand_value = nullptr,
-                       uint8_t *cand_sig = nullptr) {
-  LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans));
+                       uint8_t *cand_sig = nullptr, const LsgKeyHint *hint = nullptr) {
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans, hint));
   // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
   const uint2 *ident_pc = nullptr;
@@ -126,7 +126,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
     cudaStream_t main_stream = ctx->stream;
     ctx->stream = ctx->side;
     int rc = lsg_ident_classes(ctx, idents, n_idents, &ident_pc);
-    if (!rc) rc = lsg_sort_spans(ctx, spans, n_spans, idents, sorted->key, &span_perm);
+    if (!rc) rc = lsg_sort_spans(ctx, spans, n_spans, idents, n_idents, sorted->key, &span_perm);
     ctx->stream = main_stream;
     if (rc) return rc;
     LSG_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->side));
@@ -599,13 +599,15 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   LSG_CUDA(ctx, cudaMemsetAsync(a->counters_dev, 0, sizeof(lsg_counters), ctx->stream));
   uint64_t *jc_dev = nullptr;
   SortedEvents sorted;
+  LsgKeyHint hint{a->span_ts_lo, a->span_ts_hi, a->max_grp_hint};
   // the per-incident maxima (A7) are accumulated by the join's epilogue: no second pass over the span attributes
   void *acc = nullptr;
   LSG_TRY(lsg_ws(ctx, WS_FEAT, a->n_incidents * LSG_NSIG * 8, &acc));
   LSG_CUDA(ctx, cudaMemsetAsync(acc, 0, a->n_incidents * LSG_NSIG * 8, ctx->stream));
   LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, a->events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
                              fanout, nullptr, a->cand_event, a->cand_tier, a->attr_out, a->conf_out, nullptr, nullptr, &jc_dev,
-                             &sorted, (unsigned long long *)acc, a->n_incidents, a->cand_value, a->cand_sig));
+                             &sorted, (unsigned long long *)acc, a->n_incidents, a->cand_value, a->cand_sig,
+                             a->key_hint ? &hint : nullptr));
   LSG_TRY(lsg_launch_incident_finish(ctx, (const unsigned long long *)acc, a->n_incidents, a->inc_signals));
   LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
   LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
@@ -656,7 +658,8 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   if (counters_out) memcpy(counters_out, ctx->pinned, sizeof(lsg_counters));
   if (a->counters_dev) memcpy(a->counters_dev, ctx->pinned, sizeof(lsg_counters));
   if (((const lsg_counters *)ctx->pinned)->bad_idents)
-    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident is outside the identity table (n_idents=%zu)", a->n_idents);
+    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident is outside the identity table (n_idents=%zu), or the key hint does not hold",
+                    a->n_idents);
   return 0;
 }
 
@@ -767,7 +770,7 @@ int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out) {
   ctx->slot_busy[slot] = false;
   if (counters_out) memcpy(counters_out, ctx->slot_counters_host[slot], sizeof(lsg_counters));
   if (((const lsg_counters *)ctx->slot_counters_host[slot])->bad_idents)
-    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident in the batch of slot %d is outside the identity table", slot);
+    return lsg_fail(ctx, LSG_ERR_RANGE, "a record's ident in the batch of slot %d is outside the identity table, or the key hint does not hold", slot);
   return 0;
 }
 

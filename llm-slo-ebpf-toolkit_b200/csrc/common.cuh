@@ -265,8 +265,15 @@ struct EventColumns {     // events grouped by key as columns (what the join sta
 struct LsgBatchStats {
   long long ts_min, ts_max;                 // over the live events, or over the live spans (see lsg_sort_events_prepare)
   unsigned long long n_live, n_unsupported; // events; n_live only when the events were looked at before the sort
-  unsigned int max_grp, bad;                // bad: bit 0 an event's, bit 1 a span's ident is outside the identity table
+  unsigned int max_grp, bad;                // bad: bit 0 an event's, bit 1 a span's ident is outside the identity table,
+                                            // bit 2 the caller's key hint does not hold
   unsigned int pad[2];
+};
+
+// what a caller may state about a batch so that nothing has to be read back before the sort (lsg_pipeline_args.key_hint)
+struct LsgKeyHint {
+  long long span_ts_lo, span_ts_hi;   // every live span's time lies in [lo, hi]
+  unsigned int max_grp;               // no identity row has a larger group
 };
 
 struct SortedEvents {
@@ -290,13 +297,14 @@ int lsg_sort_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_iden
 // unsupported-type count and the events' ident check then come out of the sort's own first pass (stats_dev).
 // Without spans (the sort as its own entry point) one pass over the events sets the range.
 int lsg_sort_events_prepare(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans);
+                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans,
+                            const LsgKeyHint *hint);
 // want_copy false (and sorted_out NULL): only the permutation (and bins / keys) is produced, no sorted copy of the events
 int lsg_sort_events_finish(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                            lsg_event *sorted_out, SortedEvents *out, bool allow_counting, bool want_copy);
 int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, uint32_t sig,
                            const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out, size_t *n_live_out);
-int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &key,
+int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &key,
                    const uint32_t **perm_out);
 struct JoinArgs {
   const lsg_span *spans; size_t n_spans; const uint32_t *span_perm;

@@ -99,7 +99,8 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
       atomicOr((unsigned int *)&counters[5], 1u);
     } else {
       const uint32_t grp = load_ident(idents, s.ident).grp;
-      if (grp != 0 && s.ts != LSG_TS_ZERO && n_live != 0) {
+      // (a group beyond the key space can only come from a key hint that does not hold: the batch is void, stay in bounds)
+      if (grp != 0 && ((uint64_t)grp << ks.tbits) < ks.dead && s.ts != LSG_TS_ZERO && n_live != 0) {
         // The range is a function of the span's SORT KEY, not of its exact time: spans are processed in key
         // order, and the tiles below rely on a and b being non-decreasing in that order.  So take the span's
         // quantum [t0, t1] (its time clamped into the key space exactly as k_span_keys does) and search for

@@ -94,6 +94,13 @@ __device__ __forceinline__ bool event_live(const EventRec &e, const lsg_ident *i
   return *grp != 0;
 }
 
+// the caller stated the spans' time range and the largest group (LsgKeyHint): nobody waits for the statistics, they are
+// only checked against the statement; a violated one voids the batch (bit 2 of `bad`, reported with the counters)
+__global__ void k_check_hint(EventStats *st, long long lo, long long hi, unsigned int max_grp) {
+  if (st->ts_min <= st->ts_max && (st->ts_min < lo || st->ts_max > hi)) st->bad |= 4u;
+  if (st->max_grp > max_grp) st->bad |= 4u;
+}
+
 // the sort's own look at an event: its key (or "dead"), and what the batch statistics need from it
 struct EventTally {
   unsigned int unsup = 0;
@@ -115,7 +122,7 @@ __device__ __forceinline__ bool event_key(const EventRec &e, const lsg_ident *id
   if (!event_live(e, idents, n_idents, &g, &t.bad)) return false;
   if (e.ts < ks.ts_min || e.ts > ks.ts_hi) return false;   // further than the window from every span
   *key = lsg_make_key(ks, g, e.ts);
-  return true;
+  return *key < ks.dead;   // a group beyond the stated maximum (key hint that does not hold): never index past the tables
 }
 
 __global__ void __launch_bounds__(256)
@@ -178,12 +185,12 @@ k_event_keys(const lsg_event *__restrict__ events, size_t n, const lsg_ident *__
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__restrict__ idents, KeySpec ks, int64_t ts_max,
-            KeyT *__restrict__ keys) {
+k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__restrict__ idents, uint32_t n_idents, KeySpec ks,
+            int64_t ts_max, KeyT *__restrict__ keys) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     SpanRec s = load_span(spans + i);
     KeyT k = (KeyT)ks.dead;
-    uint32_t g = load_ident(idents, s.ident).grp;   // ident range is validated by the join's caller
+    const uint32_t g = s.ident < n_idents ? load_ident(idents, s.ident).grp : 0u;   // a bad ident is reported elsewhere
     if (g != 0 && s.ts != LSG_TS_ZERO) {
       int64_t t = s.ts < ks.ts_min ? ks.ts_min : (s.ts > ts_max ? ts_max : s.ts);   // processing order only
       k = (KeyT)lsg_make_key(ks, g, t);
@@ -672,13 +679,14 @@ int bits_of(uint64_t v) {
 // Sort events by (grp, quantised time).  Fills `out`; records land in `sorted_out` (or a workspace buffer if NULL).
 int lsg_sort_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
                     int64_t window_ns, bool exact, lsg_event *sorted_out, SortedEvents *out) {
-  LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out, nullptr, 0));
+  LSG_TRY(lsg_sort_events_prepare(ctx, events, n, idents, n_idents, window_ns, exact, out, nullptr, 0, nullptr));
   return lsg_sort_events_finish(ctx, events, n, idents, n_idents, sorted_out, out, !exact, true);
 }
 
 // phase 1: one pass over the events for the key layout (time range, group count) and the analytic counters
 int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
-                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans) {
+                            int64_t window_ns, bool exact, SortedEvents *out, const lsg_span *spans, size_t n_spans,
+                            const LsgKeyHint *hint) {
   memset(out, 0, sizeof *out);
   out->n = n;
   if (n >= ((size_t)1 << 32)) return lsg_fail(ctx, LSG_ERR_RANGE, "n_events %zu does not fit 32-bit indices", n);
@@ -707,9 +715,20 @@ int lsg_sort_events_prepare(lsg_ctx *ctx, const lsg_event *events, size_t n, con
     LSG_LAUNCH_CHECK(ctx);
   }
   }
-  LSG_CUDA(ctx, cudaMemcpyAsync(pin, st_dev, sizeof init, cudaMemcpyDeviceToHost, ctx->stream));
-  LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  EventStats st = *pin;
+  EventStats st;
+  if (from_spans && hint) {
+    // no readback and no synchronisation: the key layout follows from the caller's statement
+    k_check_hint<<<1, 1, 0, ctx->stream>>>(st_dev, hint->span_ts_lo, hint->span_ts_hi, hint->max_grp);
+    LSG_LAUNCH_CHECK(ctx);
+    st = init;
+    st.ts_min = hint->span_ts_lo;
+    st.ts_max = hint->span_ts_hi;
+    st.max_grp = hint->max_grp;
+  } else {
+    LSG_CUDA(ctx, cudaMemcpyAsync(pin, st_dev, sizeof init, cudaMemcpyDeviceToHost, ctx->stream));
+    LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    st = *pin;
+  }
   if (st.bad & 1u) return lsg_fail(ctx, LSG_ERR_RANGE, "an event's ident is outside the identity table (n_idents=%zu)", n_idents);
   if (st.bad & 2u) return lsg_fail(ctx, LSG_ERR_RANGE, "a span's ident is outside the identity table (n_idents=%zu)", n_idents);
   out->stats_dev = st_dev;
@@ -851,7 +870,7 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
 }
 
 // Processing order of the spans: same key as the events, so consecutive spans read overlapping event ranges.
-int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_ident *idents, const KeySpec &ks,
+int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &ks,
                    const uint32_t **perm_out) {
   *perm_out = nullptr;
   if (n == 0) return 0;
@@ -870,12 +889,12 @@ int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_iden
   ctx->prof = false;   // the passes of the span sort are accounted as one PK_SPAN_SORT interval
   struct Restore { lsg_ctx *c; bool v; ~Restore() { c->prof = v; } } restore{ctx, saved_prof};
   if (k32) {
-    k_span_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint32_t *)ka);
+    k_span_keys<uint32_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, (uint32_t)n_idents, ks, ts_max, (uint32_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint32_t *ko;
     LSG_TRY(radix_sort_pairs<uint32_t>(ctx, (uint32_t *)ka, (uint32_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_SPAN_HIST, &ko, &perm));
   } else {
-    k_span_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, ks, ts_max, (uint64_t *)ka);
+    k_span_keys<uint64_t><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(spans, n, idents, (uint32_t)n_idents, ks, ts_max, (uint64_t *)ka);
     LSG_LAUNCH_CHECK(ctx);
     uint64_t *ko;
     LSG_TRY(radix_sort_pairs<uint64_t>(ctx, (uint64_t *)ka, (uint64_t *)kb, (uint32_t *)ia, (uint32_t *)ib, n, ks.bits, WS_SPAN_HIST, &ko, &perm));

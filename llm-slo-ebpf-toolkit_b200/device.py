@@ -60,6 +60,18 @@ class DeviceWorkload:
             getattr(self, name).view(torch.uint8)[: src.numel()].copy_(src)
         torch.cuda.synchronize()
 
+    def state_key_range(self, span_ts_lo=None, span_ts_hi=None, max_grp=None):
+        """Tell the library the spans' time range and the largest join group (lsg_pipeline_args.key_hint): the step then
+        runs without the readback of the key layout.  Defaults: what the generator's configuration guarantees (span
+        times in [t0, t0 + horizon), one group per `pods_per_group` pods)."""
+        cfg = self.cfg
+        self.args.key_hint = 1
+        self.args.span_ts_lo = int(cfg.t0_ns if span_ts_lo is None else span_ts_lo)
+        self.args.span_ts_hi = int(cfg.t0_ns + cfg.horizon_ns - 1 if span_ts_hi is None else span_ts_hi)
+        ppg = max(int(cfg.pods_per_group), 1)
+        # the generator numbers groups from 1: identity row // pods_per_group + 1
+        self.args.max_grp_hint = int((max(self.n_idents, 1) - 1) // ppg + 1 if max_grp is None else max_grp)
+
     def step(self):
         """One pass of the hot path over the batch (asynchronous on the context's stream)."""
         self.ctx.call_dev("lsg_pipeline_dev", C.byref(self.args))

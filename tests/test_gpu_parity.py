@@ -565,3 +565,59 @@ def test_randomized_configs_vs_indexed_oracle(ctx, case):
     got = ctx.process_batch(w["spans"], w["events"], ids, window_ms * 1_000_000, thr, fanout)
     want = O.process_batch(w["spans"], w["events"], ids, window_ms * 1_000_000, thr, fanout, indexed=True, nthreads=8)
     _eq_batch(got, want)
+
+
+def test_stated_key_range_skips_the_readback_and_is_checked(ctx):
+    """lsg_pipeline_args.key_hint: the caller states the spans' time range and the largest group; results are those
+    of the un-hinted run, a statement that does not hold voids the batch (counters.bad_idents)."""
+    import torch
+    from llm_slo_ebpf_toolkit_b200.device import DeviceWorkload
+    cfg = synth.config(300_000, 30_000, 32, 8, 2, seed=9, horizon_ns=100_000_000_000, multi_fault=1)
+    plain = DeviceWorkload(ctx, cfg)
+    plain.step()
+    torch.cuda.synchronize()
+    want = plain.read_counters()
+    assert want.bad_idents == 0
+    hinted = DeviceWorkload(ctx, cfg)
+    hinted.state_key_range()
+    for _ in range(3):                       # back to back without a host synchronisation in between
+        hinted.step()
+    torch.cuda.synchronize()
+    got = hinted.read_counters()
+    assert bytes(got) == bytes(want)
+    for name, dt in (("cand_event", np.uint32), ("cand_tier", np.uint8), ("top1", np.uint8)):
+        assert np.array_equal(hinted.host(name, dt), plain.host(name, dt)), name
+    assert np.array_equal(hinted.host("attr", np.float64), plain.host("attr", np.float64), equal_nan=True)
+    assert np.array_equal(hinted.host("posterior", np.float64), plain.host("posterior", np.float64), equal_nan=True)
+    # a wider statement is still true: same results
+    hinted.state_key_range(span_ts_lo=cfg.t0_ns - 10**12, span_ts_hi=cfg.t0_ns + cfg.horizon_ns + 10**12, max_grp=1000)
+    hinted.step()
+    torch.cuda.synchronize()
+    assert bytes(hinted.read_counters()) == bytes(want)
+    # statements that do not hold: a time range that ends too early, a group bound that is too small
+    hinted.state_key_range(span_ts_hi=cfg.t0_ns + cfg.horizon_ns // 2)
+    hinted.step()
+    torch.cuda.synchronize()
+    assert hinted.read_counters().bad_idents != 0
+    hinted.state_key_range(max_grp=3)
+    hinted.step()
+    torch.cuda.synchronize()
+    assert hinted.read_counters().bad_idents != 0
+    hinted.state_key_range()
+    hinted.step()
+    torch.cuda.synchronize()
+    assert bytes(hinted.read_counters()) == bytes(want)
+    # with the statement nothing is validated up front: bad idents must stay in bounds and surface in the counters
+    w = synth.generate_host(cfg)
+    for field in ("spans", "events"):
+        bad = dict(w)
+        bad[field] = w[field].copy()
+        bad[field]["ident"][123] = 0x7FFFFFFF
+        hinted.upload(bad)
+        hinted.step()
+        torch.cuda.synchronize()
+        assert hinted.read_counters().bad_idents != 0, field
+    hinted.upload(w)
+    hinted.step()
+    torch.cuda.synchronize()
+    assert bytes(hinted.read_counters()) == bytes(want)
