@@ -342,7 +342,11 @@ def main():
                                           outs["inc_signals"].data_ptr(), outs["posterior"].data_ptr(), outs["top1"].data_ptr(),
                                           outs["counters"].data_ptr(), None if dense else outs["cand_value"].data_ptr(),
                                           None if dense else outs["cand_sig"].data_ptr())
-                slots.append((host, outs, {"dense": make(True), "compact": make(False)}))
+                forms = {"dense": make(True), "compact": make(False)}
+                for a_ in forms.values():   # the same statement about the batch as in the device-resident steps
+                    a_.key_hint, a_.max_grp_hint = wl.args.key_hint, wl.args.max_grp_hint
+                    a_.span_ts_lo, a_.span_ts_hi = wl.args.span_ts_lo, wl.args.span_ts_hi
+                slots.append((host, outs, forms))
             h2d = sum(slots[0][0][k].numel() for k in slots[0][0])
             common = ("cand_event", "cand_tier", "inc_signals", "posterior", "top1", "counters")
             d2h = {"dense": sum(slots[0][1][k].numel() for k in common + ("attr", "conf")),
