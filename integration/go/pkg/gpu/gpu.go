@@ -259,3 +259,66 @@ func (c *Ctx) SegmentQuantiles(values []float64, segment []uint32, nSegments int
 		C.size_t(nSegments), (*C.double)(ptr(q)), C.size_t(len(q)), (*C.double)(ptr(out)), (*C.uint64_t)(ptr(cnt)))
 	return out, cnt, c.err(rc)
 }
+
+// PipelineResult is what one lsg_pipeline call returns for a batch of spans grouped into incidents: the kept candidates
+// per span in compact form (event index, tier, signal, value: a span's attribute map is max(value) per signal over
+// them, its confidence TierConfidence[CandTier[first]]), the per-incident signal maxima, posteriors and top-1 labels,
+// and the batch counters (debug stats, confusion matrix, accuracy numerators).
+type PipelineResult struct {
+	Fanout     int
+	CandEvent  []uint32
+	CandTier   []uint8
+	CandSig    []uint8 // 0xff = empty slot
+	CandValue  []float64
+	IncSignals []float64 // n_incidents * NSig, NaN = absent
+	Posterior  []float64 // n_incidents * NDom
+	Top1       []uint8
+	Counters   Counters
+}
+
+// Counters is lsg_counters.
+type Counters struct {
+	Debug                                   Debug
+	Confusion                               Confusion
+	Events, Spans, Incidents, Candidates, Kept uint64
+	BadIdents                               uint64
+}
+
+// KeyHint is the optional statement about a batch (lsg_pipeline_args.key_hint): every span that can match has its time in
+// [SpanTsLo, SpanTsHi] and no identity row's group exceeds MaxGrp.  With it the library never synchronises mid-call.
+type KeyHint struct {
+	SpanTsLo, SpanTsHi int64
+	MaxGrp             uint32
+}
+
+// Pipeline runs ProcessBatch + the per-incident maxima + BuildAttributionsBayes + BuildConfusionMatrix for one batch in
+// one call (processor.go:29, pipeline.go:31,65).  Spans carry their incident index; incActual / incExpected /
+// incExpectedN are encoded as for ConfusionCounts.
+func (c *Ctx) Pipeline(spans []Span, events []Event, idents []Ident, incActual []uint8, incExpected []uint32,
+	incExpectedN []uint8, windowNS int64, threshold float64, fanout int, coverageThr float64, hint *KeyHint) (PipelineResult, error) {
+	defer c.enter()()
+	if fanout <= 0 {
+		fanout = 3
+	}
+	ns, ni := len(spans), len(incActual)
+	r := PipelineResult{Fanout: fanout, CandEvent: make([]uint32, ns*fanout), CandTier: make([]uint8, ns*fanout),
+		CandSig: make([]uint8, ns*fanout), CandValue: make([]float64, ns*fanout), IncSignals: make([]float64, ni*NSig),
+		Posterior: make([]float64, ni*NDom), Top1: make([]uint8, ni)}
+	var a C.lsg_pipeline_args
+	a.spans, a.n_spans = (*C.lsg_span)(ptr(spans)), C.size_t(ns)
+	a.events, a.n_events = (*C.lsg_event)(ptr(events)), C.size_t(len(events))
+	a.idents, a.n_idents = (*C.lsg_ident)(ptr(idents)), C.size_t(len(idents))
+	a.n_incidents = C.size_t(ni)
+	a.inc_actual, a.inc_expected = (*C.uint8_t)(ptr(incActual)), (*C.uint32_t)(ptr(incExpected))
+	a.inc_expected_n = (*C.uint8_t)(ptr(incExpectedN))
+	a.window_ns, a.threshold, a.fanout, a.coverage_thr = C.int64_t(windowNS), C.double(threshold), C.int(fanout), C.double(coverageThr)
+	a.cand_event, a.cand_tier = (*C.uint32_t)(ptr(r.CandEvent)), (*C.uint8_t)(ptr(r.CandTier))
+	a.cand_sig, a.cand_value = (*C.uint8_t)(ptr(r.CandSig)), (*C.double)(ptr(r.CandValue))
+	a.inc_signals, a.posterior, a.top1 = (*C.double)(ptr(r.IncSignals)), (*C.double)(ptr(r.Posterior)), (*C.uint8_t)(ptr(r.Top1))
+	if hint != nil {
+		a.key_hint, a.max_grp_hint = 1, C.uint32_t(hint.MaxGrp)
+		a.span_ts_lo, a.span_ts_hi = C.int64_t(hint.SpanTsLo), C.int64_t(hint.SpanTsHi)
+	}
+	rc := C.lsg_pipeline(c.h, &a, (*C.lsg_counters)(unsafe.Pointer(&r.Counters)))
+	return r, c.err(rc)
+}
