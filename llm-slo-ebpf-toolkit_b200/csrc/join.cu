@@ -19,9 +19,13 @@
 //   k_ident_class_*  per identity row (pod, class of its (service, node) pair), so that a (span, event) pair
 //                  compares two words instead of loading two identity rows.
 //   k_join_tiles   a CTA takes 128 consecutive spans.  Their ranges overlap heavily (each event is inside
-//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges — five columns,
-//                  24 B/event — into shared memory once with TMA bulk copies (cp.async.bulk + mbarrier) and
-//                  rewrites the identity column to (pod, class) in place.  Tier 1 is a tile-local hash join
+//                  ~35 spans' windows at C2), so the CTA stages the union of the ranges into shared memory
+//                  once, as six columns (time, pod, class, pid, conn, trace|signal: 28 B/event).  FUSED (what the
+//                  pipeline runs): there is no sorted copy of the events; each thread reads its permutation entries
+//                  and then the records themselves (256-bit loads, four in flight), writes the columns and probes
+//                  the trace-id hash while the record is in registers.  Unfused (LSG_JOIN_SORTED_COPY): TMA bulk
+//                  copies (cp.async.bulk + mbarrier) of the sorted columns, then the identity column is rewritten
+//                  to (pod, class) in place and a second pass probes the hash.  Tier 1 is that tile-local hash join
 //                  (every tile event probes a hash of the chunk's span trace ids once).  Tiers 2-4 are decided
 //                  by two threads per span out of shared memory; where every event of the tile carries one
 //                  class and the service+node tier is below the threshold, that tier is counted (whole quanta
