@@ -182,7 +182,9 @@ int lsg_match_pairs_dev(lsg_ctx *ctx, const lsg_span *spans, const lsg_event *ev
  *  cand_event  [n_spans*fanout] index into `events` of the kept candidates in reference order
  *              (confidence desc, |dt| asc, input order), LSG_NONE = none
  *  cand_tier   [n_spans*fanout] tier of each kept candidate, 0 = none
- *  attr_base   [n_spans*12] or NULL: SpanRecord.Attributes on entry, NaN = absent
+ *  attr_base   [n_spans*12] or NULL: SpanRecord.Attributes on entry, NaN = absent.  NaN is this ABI's "absent": an
+ *              event VALUE that is NaN is outside the parity claim (the reference keeps an existing NaN,
+ *              correlator.go:109; here a later candidate replaces it)
  *  attr_out    [n_spans*12] enriched attributes, NaN = absent (correlator.go:106-112)
  *  conf_out    [n_spans] llm.ebpf.correlation_confidence, 0 = not set (correlator.go:113-118)
  *  retrieval_out [n_spans] or NULL: DecomposeRetrieval total (attribute is set when > 0)
@@ -216,13 +218,17 @@ int lsg_incident_features_dev(lsg_ctx *ctx, const double *span_attr, const uint3
  * already belongs to its own pool, or a service that cannot take the device-wide synchronisation cudaMalloc and
  * cudaFree imply while other streams are running.  It needs no lsg_ctx and calls no cudaMalloc, cudaFree or other
  * allocating routine: the accumulators are a fixed array inside the library image (LSG_STATIC_MAX_INCIDENTS x 12
- * x 8 bytes = 1.5 MiB of device memory on every GPU that loads the library, held until the process exits).
+ * x 8 bytes = 1.5 MiB of device memory per GPU, taken when the driver first loads this part of the library on that
+ * GPU - under CUDA's default lazy loading that is this function's first call there - and held until the process
+ * exits).  Make that first call on each device before handing the remaining device memory to your own pool
+ * (or run with CUDA_MODULE_LOADING=EAGER).
  *   - all pointers are DEVICE pointers on the CURRENT device; `stream` is a cudaStream_t of that device (NULL = the
  *     default stream).  The work is enqueued on `stream` and the call returns without synchronising.
  *   - n_incidents > LSG_STATIC_MAX_INCIDENTS is refused with LSG_ERR_RANGE; split the batch or use the
  *     allocating entry point.
  *   - the first call on each device looks up the array's address on that device; make that first call before
- *     starting any stream capture.
+ *     starting any stream capture.  Device ordinals 0..63 are supported (LSG_ERR_RANGE beyond).
+ *   - the return value also reports a sticky CUDA error left on the device by an earlier, unrelated launch.
  *   - every call on a device shares the one array and begins by clearing the part it uses, so the previous call's
  *     values never leak in, but two calls whose work overlaps on the same GPU (different streams or threads)
  *     race on it: keep calls on one device stream-ordered.

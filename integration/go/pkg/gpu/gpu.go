@@ -304,6 +304,21 @@ func (c *Ctx) Pipeline(spans []Span, events []Event, idents []Ident, incActual [
 	r := PipelineResult{Fanout: fanout, CandEvent: make([]uint32, ns*fanout), CandTier: make([]uint8, ns*fanout),
 		CandSig: make([]uint8, ns*fanout), CandValue: make([]float64, ns*fanout), IncSignals: make([]float64, ni*NSig),
 		Posterior: make([]float64, ni*NDom), Top1: make([]uint8, ni)}
+	// `a` holds pointers into Go slices, so passing &a alone would break the cgo pointer rule ("Go pointer to
+	// unpinned Go pointer"): every slice the struct names is pinned for the duration of the call (Go >= 1.21).
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	pinned := func(p unsafe.Pointer) unsafe.Pointer {
+		if p != nil {
+			pin.Pin(p)
+		}
+		return p
+	}
+	for _, p := range []unsafe.Pointer{ptr(spans), ptr(events), ptr(idents), ptr(incActual), ptr(incExpected),
+		ptr(incExpectedN), ptr(r.CandEvent), ptr(r.CandTier), ptr(r.CandSig), ptr(r.CandValue), ptr(r.IncSignals),
+		ptr(r.Posterior), ptr(r.Top1)} {
+		pinned(p)
+	}
 	var a C.lsg_pipeline_args
 	a.spans, a.n_spans = (*C.lsg_span)(ptr(spans)), C.size_t(ns)
 	a.events, a.n_events = (*C.lsg_event)(ptr(events)), C.size_t(len(events))

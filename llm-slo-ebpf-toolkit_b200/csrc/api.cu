@@ -587,9 +587,11 @@ int lsg_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *predicted,
 int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   if (!ctx || !a) return LSG_ERR_INVALID;
   // attr_out, conf_out, cand_value and cand_sig are optional outputs
-  if (!a->spans || !a->events || !a->idents || !a->cand_event || !a->cand_tier ||
-      !a->inc_signals || !a->posterior || !a->top1 || !a->counters_dev || !a->inc_actual || !a->inc_expected ||
-      !a->inc_expected_n)
+  // an empty array may be NULL (a Go caller's empty slice): ProcessBatch with no signals returns the spans unchanged
+  if ((a->n_spans && (!a->spans || !a->cand_event || !a->cand_tier)) || (a->n_events && !a->events) ||
+      ((a->n_spans || a->n_events) && !a->idents) || !a->counters_dev ||
+      (a->n_incidents && (!a->inc_signals || !a->posterior || !a->top1 || !a->inc_actual || !a->inc_expected ||
+                          !a->inc_expected_n)))
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
   LSG_TRY(set_device(ctx));
   int64_t window_ns = a->window_ns;
@@ -622,7 +624,8 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
 // makes the copies asynchronous); inputs go up, the pipeline runs, results come back, then it synchronises.
 int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counters_out) {
   if (!ctx || !a) return LSG_ERR_INVALID;
-  if (!a->spans || !a->events || !a->idents || !a->inc_actual || !a->inc_expected || !a->inc_expected_n)
+  if ((a->n_spans && !a->spans) || (a->n_events && !a->events) || ((a->n_spans || a->n_events) && !a->idents) ||
+      (a->n_incidents && (!a->inc_actual || !a->inc_expected || !a->inc_expected_n)))
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
   LSG_TRY(set_device(ctx));
   const int f = a->fanout <= 0 ? 3 : a->fanout;
@@ -699,7 +702,8 @@ extern "C" {
 
 int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   if (!ctx || !a || slot < 0 || slot > 1) return LSG_ERR_INVALID;
-  if (!a->spans || !a->events || !a->idents || !a->inc_actual || !a->inc_expected || !a->inc_expected_n)
+  if ((a->n_spans && !a->spans) || (a->n_events && !a->events) || ((a->n_spans || a->n_events) && !a->idents) ||
+      (a->n_incidents && (!a->inc_actual || !a->inc_expected || !a->inc_expected_n)))
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
   if (ctx->slot_busy[slot]) return lsg_fail(ctx, LSG_ERR_INVALID, "slot %d is still in flight: call lsg_pipeline_wait first", slot);
   LSG_TRY(set_device(ctx));

@@ -260,8 +260,11 @@ int lsg_launch_confusion(lsg_ctx *ctx, const uint8_t *actual, const uint8_t *pre
 // handed the device's whole memory budget to its own pool has nothing left for cudaMalloc to give, and a
 // service that keeps other streams busy cannot afford cudaMalloc/cudaFree, which synchronise the whole
 // device.  For them the accumulators below live in the library image itself: a fixed array in device
-// global memory, present on every GPU that loads the library from load until exit
-// (LSG_STATIC_MAX_INCIDENTS x 12 x 8 bytes = 1.5 MiB per GPU), so the entry point never allocates.
+// global memory that belongs to this file's CUDA module (LSG_STATIC_MAX_INCIDENTS x 12 x 8 bytes = 1.5 MiB per
+// GPU), so the entry point never allocates.  With CUDA's default lazy module loading the driver places the module,
+// array included, on a GPU at the first symbol lookup or kernel launch from this file on that GPU and keeps it
+// until the process exits: that first use is the one moment device memory is taken, so it belongs before a
+// caller gives the rest of the device to its own pool (or run with CUDA_MODULE_LOADING=EAGER).
 static __device__ __align__(256) unsigned long long g_static_incident_keys[(size_t)LSG_STATIC_MAX_INCIDENTS * LSG_NSIG];
 
 namespace {
@@ -297,9 +300,14 @@ extern "C" int lsg_incident_signals_static(void *stream, const double *span_attr
   if (n_incidents == 0) return 0;
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) {
+  if (e != cudaSuccess || dev < 0) {
     static_err(errbuf, errbuf_len, "no current CUDA device (cudaGetDevice: %s)", cudaGetErrorString(e));
-    return e == cudaSuccess ? LSG_ERR_INVALID : LSG_ERR_NODEVICE;
+    return LSG_ERR_NODEVICE;
+  }
+  if (dev >= kStaticMaxDevices) {
+    static_err(errbuf, errbuf_len, "device ordinal %d is beyond the %d devices this entry point keeps an address for",
+               dev, kStaticMaxDevices);
+    return LSG_ERR_RANGE;
   }
   unsigned long long *keys = nullptr;
   int sms = 0;
@@ -341,9 +349,10 @@ extern "C" int lsg_incident_signals_static(void *stream, const double *span_attr
     k_incident_accumulate<<<blocks_for(n_spans * LSG_NSIG), 256, 0, st>>>(span_attr, span_incident, nullptr, n_spans,
                                                                         n_incidents, keys, nullptr);
   k_incident_finish<<<blocks_for(n), 256, 0, st>>>(keys, n, signals_out);
-  e = cudaGetLastError();
+  e = cudaGetLastError();   // also reports (and clears) a sticky error left by an earlier, unrelated launch
   if (e != cudaSuccess) {
-    static_err(errbuf, errbuf_len, "kernel launch failed: %s", cudaGetErrorString(e));
+    static_err(errbuf, errbuf_len, "kernel launch failed (or an earlier launch on this device left an error): %s",
+               cudaGetErrorString(e));
     return LSG_ERR_CUDA;
   }
   return 0;

@@ -94,6 +94,10 @@ k_span_ranges(const lsg_span *__restrict__ spans, const uint32_t *__restrict__ s
               uint32_t n_idents, int64_t W, uint4 *__restrict__ ranges, uint4 *__restrict__ ranges2,
               unsigned long long *__restrict__ counters) {
   const uint64_t ts_max_q = ((uint64_t)1 << ks.tbits) - 1;
+  // counting sort: only the placed events have a permutation entry, and bins[dead] is their number.  A span that can
+  // match nothing gets the empty range at that position, so a tile that holds it never reads past the written part
+  // of the permutation (the host's n_live is only an upper bound on that path).
+  if (bins) n_live = bins[(uint32_t)ks.dead];
   for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_spans; q += (size_t)gridDim.x * blockDim.x) {
     const size_t si = span_perm ? span_perm[q] : q;
     const SpanRec s = load_span(spans + si);
@@ -1034,7 +1038,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   const bool t32 = a.ev.key.shift < 29 && wi + ((int64_t)2 << a.ev.key.shift) < ((int64_t)1 << 31);
   // no sorted copy of the events (lsg_sort_events_finish was told not to gather): the kernels read through the permutation
   const bool fused = a.ev.col.ts == nullptr;
-  if (fused && !a.events_in) return lsg_fail(ctx, LSG_ERR_INVALID, "join without sorted columns needs the input records");
+  if (fused && !a.events_in && a.ev.n != 0)
+    return lsg_fail(ctx, LSG_ERR_INVALID, "join without sorted columns needs the input records");
   if (a.fanout <= 3) {
     if (fused) { if (t32) LSG_TRY(launch(k_join_tiles<3, true, true>)); else LSG_TRY(launch(k_join_tiles<3, false, true>)); }
     else { if (t32) LSG_TRY(launch(k_join_tiles<3, true, false>)); else LSG_TRY(launch(k_join_tiles<3, false, false>)); }
