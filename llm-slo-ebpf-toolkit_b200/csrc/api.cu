@@ -117,6 +117,45 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        unsigned long long *inc_keys = nullptr, size_t n_incidents = 0, double *cand_value = nullptr,
                        uint8_t *cand_sig = nullptr, const LsgKeyHint *hint = nullptr) {
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans, hint));
+  void *small_v;
+  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
+  // Default path: the records are moved once into (group, time slab) buckets and the slab join stages contiguous
+  // tiles (sort.cu "bucket partition", join_slab.cuh).  LSG_JOIN_PATH=perm keeps the permutation sort + gathering join
+  // (also taken when the bucket tables would be out of proportion to the batch).
+  static const char *path_env = getenv("LSG_JOIN_PATH");
+  const KeySpec bk = lsg_bucket_keyspec(sorted->key, n_events, window_ns);
+  if (!(path_env && strcmp(path_env, "perm") == 0) && lsg_bucket_path_ok(bk, n_events, n_spans, window_ns, fanout)) {
+    Bucketed bev, bsp;
+    const uint2 *ident_pc = nullptr;
+    {
+      LSG_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+      LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0));
+      cudaStream_t main_stream = ctx->stream;
+      ctx->stream = ctx->side;   // identity classes and the spans' partition run next to the events' partition
+      int rc = lsg_ident_classes(ctx, idents, n_idents, &ident_pc);
+      if (!rc) rc = lsg_bucket_spans(ctx, spans, n_spans, idents, n_idents, bk, &bsp);
+      ctx->stream = main_stream;
+      if (rc) return rc;
+      LSG_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->side));
+    }
+    LSG_TRY(lsg_bucket_events(ctx, events, n_events, idents, n_idents, bk, const_cast<LsgBatchStats *>(sorted->stats_dev), &bev));
+    LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    ctx->last_key = bk;
+    JoinArgs ja;
+    memset(&ja, 0, sizeof ja);
+    ja.spans = spans; ja.n_spans = n_spans;
+    ja.ev = *sorted; ja.events_in = events; ja.idents = idents; ja.n_idents = n_idents;
+    ja.window_ns = window_ns; ja.threshold = threshold; ja.fanout = fanout;
+    ja.attr_base = attr_base; ja.cand_event = cand_event; ja.cand_tier = cand_tier; ja.attr_out = attr_out;
+    ja.conf_out = conf_out; ja.retrieval_out = retrieval_out; ja.n_cand_out = n_cand_out;
+    ja.counters = (uint64_t *)((char *)small_v + SMALL_JOIN);
+    ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
+    ja.ident_pc = ident_pc;
+    ja.cand_value = cand_value; ja.cand_sig = cand_sig;
+    LSG_TRY(lsg_launch_join_slab(ctx, ja, bev, bsp));
+    *join_counters_dev = ja.counters;
+    return 0;
+  }
   // the span sort only needs the key layout: it runs on the side stream while the event sort runs on the main one
   const uint32_t *span_perm = nullptr;
   const uint2 *ident_pc = nullptr;
@@ -136,8 +175,6 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   static const bool sorted_copy = getenv("LSG_JOIN_SORTED_COPY") != nullptr;
   LSG_TRY(lsg_sort_events_finish(ctx, events, n_events, idents, n_idents, nullptr, sorted, true, sorted_copy));
   LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
-  void *small_v;
-  LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
   JoinArgs ja;
   ja.spans = spans; ja.n_spans = n_spans; ja.span_perm = span_perm;
   ja.ev = *sorted; ja.events_in = events; ja.idents = idents; ja.n_idents = n_idents;
@@ -267,7 +304,8 @@ void lsg_destroy(lsg_ctx *ctx) {
 // ---- per-kernel timing ------------------------------------------------------------------------------
 static const char *kProfNames[PK_COUNT] = {"event_stats", "event_keys", "radix_hist", "radix_scan", "radix_scatter",
                                            "gather_events", "span_sort", "join", "incident_features", "attribute",
-                                           "confusion", "match_pairs", "span_ranges"};
+                                           "confusion", "match_pairs", "span_ranges", "bucket_count", "bucket_scatter",
+                                           "bucket_spans", "tile_list"};
 int lsg_profile_enable(lsg_ctx *ctx, int on) {
   if (!ctx) return LSG_ERR_INVALID;
   ctx->prof = on != 0;

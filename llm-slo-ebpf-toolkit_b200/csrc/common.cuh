@@ -47,6 +47,16 @@ enum {
   WS_SCAN,           // counting sort: block sums of the scan
   WS_IDENT_PC,       // join: (pod, service+node class) per identity row
   WS_IDENT_TABLE,    // join: hash table that numbers the (service, node) classes
+  WS_BK_EV,          // bucket partition: events grouped by (group, time slab) bucket
+  WS_BK_EV_ORIG,     // ... their input indices
+  WS_BK_EV_ENDS,     // ... bucket ends (and, before the scatter, counts / starts)
+  WS_BK_SP,          // the same three for the spans
+  WS_BK_SP_ORIG,
+  WS_BK_SP_ENDS,
+  WS_BK_TMP,         // two-level partition: records grouped by super-bucket
+  WS_BK_TMP_ORIG,
+  WS_BK_SUPER,       // two-level partition: super-bucket cursors
+  WS_TILES,          // slab join: tile list
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
   WS_PIPE_END = WS_PIPE + 2 * 16 - 1,
   WS_COUNT
@@ -93,7 +103,7 @@ struct KeySpec {
 // per-kernel timing (bench.py's roofline): CUDA events recorded on the context's stream around each launch
 enum {
   PK_STATS = 0, PK_KEYS, PK_HIST, PK_SCAN, PK_SCATTER, PK_GATHER, PK_SPAN_SORT, PK_JOIN, PK_FEATURES, PK_ATTRIBUTE,
-  PK_CONFUSION, PK_PAIRS, PK_RANGES, PK_COUNT
+  PK_CONFUSION, PK_PAIRS, PK_RANGES, PK_BK_COUNT, PK_BK_SCATTER, PK_BK_SPANS, PK_TILES, PK_COUNT
 };
 struct ProfSpan { int kind; cudaEvent_t a, b; };
 
@@ -306,6 +316,27 @@ int lsg_sort_signal_by_pod(lsg_ctx *, const lsg_event *events, size_t n, const l
                            const uint64_t **keys_out, const uint32_t **perm_out, KeySpec *ks_out, size_t *n_live_out);
 int lsg_sort_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &key,
                    const uint32_t **perm_out);
+// ---- bucket partition (sort.cu) ---------------------------------------------------------------------
+// The 32-byte records are moved ONCE into coarse buckets: bucket = sort key >> LSG_BUCKET_SHIFT, i.e. one join group
+// x 64 consecutive time quanta (longer than the window, at most twice as long).  Inside a bucket the order is
+// whatever the cursor atomics gave; the slab join orders a tile by time quantum in shared memory when it stages it.
+constexpr uint32_t LSG_BUCKET_SHIFT = 6;
+struct Bucketed {
+  const void *rec;         // lsg_event / lsg_span records grouped by bucket
+  const uint32_t *orig;    // position -> input index
+  const uint32_t *ends;    // ends[b] = one past the last record of bucket b; ends[-1] = 0 is readable
+  uint32_t n_buckets;      // buckets of records that can match; for spans bucket n_buckets holds the ones that cannot
+  KeySpec key;
+};
+// key layout of the bucket path derived from the sort's (coarser quantum for sparse batches, tbits >= bucket shift)
+KeySpec lsg_bucket_keyspec(const KeySpec &ks, size_t n_events, int64_t window_ns);
+bool lsg_bucket_path_ok(const KeySpec &bk, size_t n_events, size_t n_spans, int64_t window_ns, int fanout);
+// stats_dev: the first pass adds the unsupported-type count and the ident check of the events (NULL: not wanted)
+int lsg_bucket_events(lsg_ctx *, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &bk,
+                      LsgBatchStats *stats_dev, Bucketed *out);
+int lsg_bucket_spans(lsg_ctx *, const lsg_span *spans, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &bk,
+                     Bucketed *out);
+
 struct JoinArgs {
   const lsg_span *spans; size_t n_spans; const uint32_t *span_perm;
   SortedEvents ev; const lsg_event *events_in; const lsg_ident *idents; size_t n_idents;
@@ -319,6 +350,9 @@ struct JoinArgs {
   double *cand_value; uint8_t *cand_sig;   // optional: value and signal of every kept candidate, [n_spans * fanout]
 };
 int lsg_launch_join(lsg_ctx *, const JoinArgs &);
+// the slab join: events and spans bucketed by lsg_bucket_*; the JoinArgs fields about the sorted events (ev, span_perm)
+// are not used, events_in / spans are the caller's arrays (outputs are indexed by input position)
+int lsg_launch_join_slab(lsg_ctx *, const JoinArgs &, const Bucketed &ev, const Bucketed &sp);
 // per identity row: x = pod id, y = class of its (service, node) pair (0 when either is empty; equal pairs get
 // equal classes), so that the join compares two words per (span, event) pair instead of loading identity rows
 int lsg_ident_classes(lsg_ctx *, const lsg_ident *idents, size_t n_idents, const uint2 **out);

@@ -958,6 +958,8 @@ k_ident_class_emit(const lsg_ident *__restrict__ idents, uint32_t n, const unsig
   }
 }
 
+#include "join_slab.cuh"
+
 }  // namespace
 
 int lsg_ident_classes(lsg_ctx *ctx, const lsg_ident *idents, size_t n_idents, const uint2 **out) {
@@ -1057,6 +1059,97 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
     if (blocks > cap) blocks = cap;
     if (fused) k_join_big<true><<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
     else k_join_big<false><<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
+  }
+  LSG_LAUNCH_CHECK(ctx);
+  return 0;
+}
+
+// ---- the slab join on bucketed records (join_slab.cuh) -------------------------------------------------------------
+bool lsg_bucket_path_ok(const KeySpec &bk, size_t n_events, size_t n_spans, int64_t window_ns, int fanout) {
+  (void)window_ns; (void)fanout;
+  if (n_events >= ((size_t)1 << 32) || n_spans >= ((size_t)1 << 32)) return false;
+  const uint64_t nbk = bk.dead >> LSG_BUCKET_SHIFT;
+  if (nbk > ((uint64_t)1 << 24)) return false;                       // tables of at most 64 MB
+  if (nbk > 4 * (uint64_t)(n_events + n_spans) + 65536) return false;   // group ids far sparser than the records
+  return true;
+}
+
+int lsg_launch_join_slab(lsg_ctx *ctx, const JoinArgs &a, const Bucketed &ev, const Bucketed &sp) {
+  LSG_CUDA(ctx, cudaMemsetAsync(a.counters, 0, 8 * sizeof(uint64_t), ctx->stream));
+  if (a.n_spans == 0) return 0;
+  SlabParams p;
+  memset(&p, 0, sizeof p);
+  JoinParams &j = p.j;
+  j.spans = a.spans; j.n_spans = a.n_spans; j.events_in = a.events_in;
+  j.idents = a.idents; j.n_idents = (uint32_t)a.n_idents;
+  j.ident_pc = a.ident_pc;
+  if (!j.ident_pc) LSG_TRY(lsg_ident_classes(ctx, a.idents, a.n_idents, &j.ident_pc));
+  j.window_ns = a.window_ns; j.threshold = a.threshold; j.fanout = a.fanout;
+  j.attr_base = a.attr_base; j.cand_event = a.cand_event; j.cand_tier = a.cand_tier; j.attr_out = a.attr_out;
+  j.conf_out = a.conf_out; j.retrieval_out = a.retrieval_out; j.n_cand_out = a.n_cand_out;
+  j.cand_value = a.cand_value; j.cand_sig = a.cand_sig;
+  j.counters = (unsigned long long *)a.counters;
+  j.inc_keys = a.inc_keys; j.n_incidents = a.n_incidents;
+  p.ev = (const lsg_event *)ev.rec; p.ev_orig = ev.orig; p.ev_ends = ev.ends;
+  p.sp = (const lsg_span *)sp.rec; p.sp_orig = sp.orig; p.sp_ends = sp.ends;
+  p.n_buckets = ev.n_buckets;
+  p.ks = ev.key;
+  p.gshift = ev.key.tbits - LSG_BUCKET_SHIFT;
+  // tile list: cuts of about equal weight, plus the chunks of spans that can match nothing
+  const size_t n_ev = a.ev.n;
+  const uint32_t n_cuts = (uint32_t)((n_ev + (size_t)JS_SPAN_WEIGHT * a.n_spans) / JS_TILE_TARGET + 2);
+  const uint32_t n_dead_chunks = (uint32_t)(a.n_spans / JS_CH + 1);
+  void *tv = nullptr, *bv = nullptr;
+  LSG_TRY(lsg_ws(ctx, WS_TILES, 64 + ((size_t)n_cuts + n_dead_chunks) * sizeof(uint2), &tv));
+  LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * sizeof(uint32_t) + 64, &bv));
+  uint32_t *hdr = (uint32_t *)tv;   // [0] tiles listed, [1] tiles taken
+  uint2 *tiles = (uint2 *)((char *)tv + 64);
+  p.tiles = tiles; p.n_tiles = hdr; p.next_tile = hdr + 1;
+  uint32_t *big_list = (uint32_t *)bv;
+  unsigned int *big_count = (unsigned int *)(a.counters + 6);
+  {
+    ProfScope ps(ctx, PK_TILES);
+    LSG_CUDA(ctx, cudaMemsetAsync(hdr, 0, 64, ctx->stream));
+    const uint32_t n_thr = n_cuts + n_dead_chunks;
+    k_slab_tiles<<<(n_thr + 255) / 256, 256, 0, ctx->stream>>>(ev.ends, sp.ends, p.n_buckets, n_cuts, tiles, hdr);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  ProfScope ps(ctx, PK_JOIN);
+  const int64_t quantum = (int64_t)1 << ev.key.shift;
+  const bool t32 = ev.key.shift < 31 && a.window_ns + quantum < ((int64_t)1 << 31);
+  // two CTAs per SM: each takes half of the shared memory an SM can give, the tile capacity follows from it
+  int dev_smem = 0, dev_resv = 0;
+  LSG_CUDA(ctx, cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device));
+  LSG_CUDA(ctx, cudaDeviceGetAttribute(&dev_resv, cudaDevAttrReservedSharedMemoryPerBlock, ctx->device));
+  const size_t fixed = (sizeof(SlabFixed) + 15) & ~(size_t)15;
+  size_t budget = (size_t)dev_smem / 2 - (size_t)dev_resv - 256;
+  uint32_t cap = (uint32_t)((budget - fixed) / slab_bytes_per_event(t32));
+  if (cap > 4088) cap = 4088;   // a note keeps the tile position in 12 bits
+  cap &= ~7u;
+  p.cap = cap;
+  const size_t smem = fixed + (size_t)cap * slab_bytes_per_event(t32) + 16;
+  auto launch = [&](auto kernel) -> int {
+    LSG_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    LSG_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, JS_THREADS, smem));
+    if (occ < 1) occ = 1;
+    kernel<<<(unsigned)(ctx->sm_count * occ), JS_THREADS, smem, ctx->stream>>>(p, big_list, big_count);
+    return 0;
+  };
+  if (a.fanout <= 3) {
+    if (t32) LSG_TRY(launch(k_join_slab<3, true>)); else LSG_TRY(launch(k_join_slab<3, false>));
+  } else if (a.fanout <= TM_MAX_F) {
+    if (t32) LSG_TRY(launch(k_join_slab<TM_MAX_F, true>)); else LSG_TRY(launch(k_join_slab<TM_MAX_F, false>));
+  } else {
+    // more kept candidates than the tile kernel holds in registers: every span goes to the warp-per-span kernel
+    k_list_bucketed_spans<<<(unsigned)std::min<size_t>((a.n_spans + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+        big_list, big_count, (uint32_t)a.n_spans);
+  }
+  LSG_LAUNCH_CHECK(ctx);
+  {
+    size_t blocks = (a.n_spans + JT_WARPS - 1) / JT_WARPS, capb = (size_t)ctx->sm_count * 4;
+    if (blocks > capb) blocks = capb;
+    k_join_big_slab<<<(unsigned)blocks, JT_THREADS, 0, ctx->stream>>>(p, big_list, big_count);
   }
   LSG_LAUNCH_CHECK(ctx);
   return 0;

@@ -903,6 +903,270 @@ int lsg_sort_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_iden
   return 0;
 }
 
+// ---- bucket partition: the records themselves, once, into coarse (group, time slab) buckets ----------------------
+// The permutation paths above leave the 32-byte records where they are and let the join gather them (random 32-byte
+// reads: ~113 B of DRAM traffic each, and the join waits on their latency).  Here the records are MOVED, once, into
+// buckets of one join group x 64 time quanta (a little longer than the window):
+//   k_bucket_count    one sequential read of the records; one no-return atomic (RED) per record on its bucket's counter
+//   k_scan_*          counts -> bucket starts
+//   k_bucket_scatter  second sequential read; slot = returning atomic on the bucket's cursor; one 256-bit store of the
+//                     record and a 4-byte store of its input index.  Records of one bucket that are in flight together
+//                     land in neighbouring slots, so the partially written 128-byte lines sit in L2 until they are
+//                     complete: DRAM sees whole lines.  That holds while a line's four arrivals are at most a few
+//                     million records apart, i.e. up to ~10^5 buckets; beyond that (1 B events: millions of buckets)
+//                     the scatter runs twice, first into <= 4096 super-buckets (runs of consecutive buckets), then,
+//                     reading those sequentially, into the buckets themselves.
+// Records that can match nothing (unsupported type, zero time, group 0, outside the spans' time range) are dropped
+// (events) or collected behind the last bucket (spans: they still get their empty outputs).
+namespace {
+
+struct EventBucketFn {
+  const lsg_ident *idents;
+  uint32_t n_idents;
+  KeySpec ks;
+  __device__ __forceinline__ bool operator()(const U8 &u, EventTally &t, uint32_t *b) const {
+    EventRec e;
+    e.ts = (int64_t)(((uint64_t)u.a.y << 32) | u.a.x);
+    e.ident = u.b.x; e.pid = u.b.y; e.conn = u.b.z; e.trace_sig = u.b.w;
+    uint64_t k;
+    if (!event_key(e, idents, n_idents, ks, t, &k)) return false;
+    *b = (uint32_t)(k >> LSG_BUCKET_SHIFT);
+    return true;
+  }
+};
+
+struct SpanBucketFn {
+  const lsg_ident *idents;
+  uint32_t n_idents;
+  KeySpec ks;
+  uint32_t n_buckets;
+  __device__ __forceinline__ bool operator()(const U8 &u, EventTally &, uint32_t *b) const {
+    const int64_t ts = (int64_t)(((uint64_t)u.a.y << 32) | u.a.x);
+    const uint32_t ident = u.a.z;
+    *b = n_buckets;   // cannot match: behind every real bucket (a bad ident is reported by k_span_stats)
+    const uint32_t g = ident < n_idents ? load_ident(idents, ident).grp : 0u;
+    if (g != 0 && ts != LSG_TS_ZERO && ts >= ks.ts_min && ts <= ks.ts_hi) {
+      const uint64_t k = lsg_make_key(ks, g, ts);
+      if (k < ks.dead) *b = (uint32_t)(k >> LSG_BUCKET_SHIFT);
+    }
+    return true;
+  }
+};
+
+template <typename Fn>
+__global__ void __launch_bounds__(256)
+k_bucket_count(const lsg_event *__restrict__ recs, size_t n, const Fn fn, uint32_t *__restrict__ counts, EventStats *st) {
+  EventTally tally;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    U8 r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(recs + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint32_t b;
+      if (fn(r[u], tally, &b)) atomicAdd(&counts[b], 1u);   // result unused: RED
+    }
+  }
+  for (; i < n; i += stride) {
+    uint32_t b;
+    if (fn(ld_nc_v8(recs + i), tally, &b)) atomicAdd(&counts[b], 1u);
+  }
+  tally.flush(st);
+}
+
+// cursor[b >> sshift] is advanced; with sshift == 0 the cursors are the bucket starts themselves and end up as the
+// bucket ends.  orig_in NULL: the records are the caller's input (index = position).
+template <typename Fn>
+__global__ void __launch_bounds__(256)
+k_bucket_scatter(const lsg_event *__restrict__ recs, const uint32_t *__restrict__ orig_in, size_t n, const Fn fn,
+                 uint32_t sshift, uint32_t *__restrict__ cursor, lsg_event *__restrict__ out, uint32_t *__restrict__ orig_out) {
+  EventTally tally;   // not flushed: the count pass already told
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    U8 r[4];
+    uint32_t b[4], slot[4], src[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(recs + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) src[u] = orig_in ? __ldg(orig_in + i + u * stride) : (uint32_t)(i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) ok[u] = fn(r[u], tally, &b[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) slot[u] = ok[u] ? atomicAdd(&cursor[b[u] >> sshift], 1u) : 0u;   // four round trips in flight
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (ok[u]) {
+        st_v8(out + slot[u], r[u]);
+        orig_out[slot[u]] = src[u];
+      }
+  }
+  for (; i < n; i += stride) {
+    const U8 r = ld_nc_v8(recs + i);
+    uint32_t b;
+    if (fn(r, tally, &b)) {
+      const uint32_t slot = atomicAdd(&cursor[b >> sshift], 1u);
+      st_v8(out + slot, r);
+      orig_out[slot] = orig_in ? orig_in[i] : (uint32_t)i;
+    }
+  }
+}
+
+// second level of the two-level partition: the input is the first level's output, whose length is only known on the
+// device (*n_dev: the last super-bucket's cursor)
+template <typename Fn>
+__global__ void __launch_bounds__(256)
+k_bucket_scatter_tail(const lsg_event *__restrict__ recs, const uint32_t *__restrict__ orig_in, const uint32_t *__restrict__ n_dev,
+                      const Fn fn, uint32_t *__restrict__ cursor, lsg_event *__restrict__ out, uint32_t *__restrict__ orig_out) {
+  EventTally tally;
+  const size_t n = *n_dev;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n; i += 4 * stride) {
+    U8 r[4];
+    uint32_t b[4], slot[4], src[4];
+    bool ok[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = ld_nc_v8(recs + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) src[u] = __ldg(orig_in + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) ok[u] = fn(r[u], tally, &b[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) slot[u] = ok[u] ? atomicAdd(&cursor[b[u]], 1u) : 0u;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (ok[u]) {
+        st_v8(out + slot[u], r[u]);
+        orig_out[slot[u]] = src[u];
+      }
+  }
+  for (; i < n; i += stride) {
+    const U8 r = ld_nc_v8(recs + i);
+    uint32_t b;
+    if (fn(r, tally, &b)) {
+      const uint32_t slot = atomicAdd(&cursor[b], 1u);
+      st_v8(out + slot, r);
+      orig_out[slot] = orig_in[i];
+    }
+  }
+}
+
+__global__ void k_super_starts(const uint32_t *__restrict__ starts, uint32_t n_super, uint32_t sshift, uint32_t *__restrict__ cur) {
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < n_super; s += gridDim.x * blockDim.x)
+    cur[s] = starts[(size_t)s << sshift];
+}
+
+constexpr uint32_t BK_SINGLE_LEVEL_MAX = 1u << 17;   // buckets a single scatter keeps line-local in L2
+constexpr uint32_t BK_SUPER_BITS = 12;               // at most 4096 super-buckets
+
+template <typename Fn>
+int bucket_partition(lsg_ctx *ctx, const void *recs, size_t n, const Fn &fn, uint32_t n_slots /* counters */,
+                     EventStats *stats_dev, int ws_rec, int ws_orig, int ws_ends, int ws_sums, int ws_tmp, int pk_count,
+                     int pk_scatter, Bucketed *out) {
+  // layout of the counter array: [0..3] zero (ends[-1] = 0), [4 .. 4 + n_slots) counts -> starts -> ends
+  void *ev, *ov, *cv, *sv;
+  LSG_TRY(lsg_ws(ctx, ws_rec, (n + 1) * 32, &ev));
+  LSG_TRY(lsg_ws(ctx, ws_orig, (n + 1) * 4, &ov));
+  LSG_TRY(lsg_ws(ctx, ws_ends, ((size_t)n_slots + 8 + SCAN_TILE) * 4, &cv));
+  const uint32_t n_blocks = (uint32_t)(((size_t)n_slots + SCAN_TILE - 1) / SCAN_TILE);
+  LSG_TRY(lsg_ws(ctx, ws_sums, (size_t)n_blocks * 4 + 64, &sv));   // (events and spans are partitioned on two streams at once)
+  uint32_t *arr = (uint32_t *)cv, *cnt = arr + 4, *sums = (uint32_t *)sv;
+  const lsg_event *in = (const lsg_event *)recs;
+  {
+    ProfScope ps(ctx, pk_count);
+    LSG_CUDA(ctx, cudaMemsetAsync(arr, 0, ((size_t)n_slots + 8) * 4, ctx->stream));
+    if (n) {
+      k_bucket_count<Fn><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(in, n, fn, cnt, stats_dev);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+    k_scan_reduce<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(cnt, n_slots, sums);
+    LSG_LAUNCH_CHECK(ctx);
+    k_scan_sums<<<1, 1024, 0, ctx->stream>>>(sums, n_blocks);
+    LSG_LAUNCH_CHECK(ctx);
+    k_scan_apply<<<n_blocks, SCAN_BLOCK, 0, ctx->stream>>>(cnt, n_slots, sums);   // cnt[b] = start of bucket b
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  if (n) {
+    ProfScope ps(ctx, pk_scatter);
+    if (n_slots <= BK_SINGLE_LEVEL_MAX) {
+      k_bucket_scatter<Fn><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(in, nullptr, n, fn, 0u, cnt, (lsg_event *)ev,
+                                                                             (uint32_t *)ov);
+      LSG_LAUNCH_CHECK(ctx);
+    } else {
+      uint32_t sshift = 0;
+      while (((n_slots - 1) >> sshift) >= (1u << BK_SUPER_BITS)) sshift++;
+      const uint32_t n_super = ((n_slots - 1) >> sshift) + 1;
+      void *tv, *tov, *suv;
+      LSG_TRY(lsg_ws(ctx, ws_tmp, (n + 1) * 32, &tv));       // three consecutive slots: records, indices, cursors
+      LSG_TRY(lsg_ws(ctx, ws_tmp + 1, (n + 1) * 4, &tov));
+      LSG_TRY(lsg_ws(ctx, ws_tmp + 2, (size_t)n_super * 4 + 64, &suv));
+      k_super_starts<<<grid_for(ctx, n_super, 256, 1), 256, 0, ctx->stream>>>(cnt, n_super, sshift, (uint32_t *)suv);
+      LSG_LAUNCH_CHECK(ctx);
+      k_bucket_scatter<Fn><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(in, nullptr, n, fn, sshift, (uint32_t *)suv,
+                                                                             (lsg_event *)tv, (uint32_t *)tov);
+      LSG_LAUNCH_CHECK(ctx);
+      // everything that was placed is now grouped by super-bucket in [0, n_placed); n_placed <= n is not known on the
+      // host, so the second pass reads a device-side count: the cursor of the last super-bucket is the total
+      // (the tail [n_placed, n) of tmp is stale: the second pass must not read it)
+      k_bucket_scatter_tail<Fn><<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>((const lsg_event *)tv, (const uint32_t *)tov,
+                                                                                  (const uint32_t *)suv + (n_super - 1), fn, cnt,
+                                                                                  (lsg_event *)ev, (uint32_t *)ov);
+      LSG_LAUNCH_CHECK(ctx);
+    }
+  }
+  out->rec = ev;
+  out->orig = (const uint32_t *)ov;
+  out->ends = cnt;
+  return 0;
+}
+
+}  // namespace
+
+KeySpec lsg_bucket_keyspec(const KeySpec &ks_in, size_t n_events, int64_t window_ns) {
+  KeySpec ks = ks_in;
+  const uint64_t max_grp = (ks.dead >> ks.tbits) - 1;
+  const uint64_t range = ks.ts_hi >= ks.ts_min ? (uint64_t)ks.ts_hi - (uint64_t)ks.ts_min : 0;
+  auto layout = [&]() {
+    ks.tbits = (uint32_t)bits_of(range >> ks.shift);
+    if (ks.tbits < LSG_BUCKET_SHIFT) ks.tbits = LSG_BUCKET_SHIFT;   // a bucket never straddles two groups
+    ks.bits = ks.tbits + (uint32_t)bits_of(max_grp + 1);
+    ks.dead = (max_grp + 1) << ks.tbits;
+  };
+  layout();
+  // a sparse batch (long time range, few events) would get millions of nearly empty buckets: coarsen the quantum
+  // until a bucket holds ~16 events on average (ranges stay supersets of the exact windows, the pairs are re-checked)
+  (void)window_ns;
+  while (ks.shift < 40 && (ks.dead >> LSG_BUCKET_SHIFT) * 16 > (uint64_t)n_events + 1024 && ks.tbits > LSG_BUCKET_SHIFT) {
+    ks.shift++;
+    layout();
+  }
+  return ks;
+}
+
+int lsg_bucket_events(lsg_ctx *ctx, const lsg_event *events, size_t n, const lsg_ident *idents, size_t n_idents,
+                      const KeySpec &bk, LsgBatchStats *stats_dev, Bucketed *out) {
+  memset(out, 0, sizeof *out);
+  out->key = bk;
+  out->n_buckets = (uint32_t)(bk.dead >> LSG_BUCKET_SHIFT);
+  EventBucketFn fn{idents, (uint32_t)n_idents, bk};
+  return bucket_partition(ctx, events, n, fn, out->n_buckets, stats_dev, WS_BK_EV, WS_BK_EV_ORIG, WS_BK_EV_ENDS, WS_SCAN, WS_BK_TMP, PK_BK_COUNT,
+                          PK_BK_SCATTER, out);
+}
+
+int lsg_bucket_spans(lsg_ctx *ctx, const lsg_span *spans, size_t n, const lsg_ident *idents, size_t n_idents, const KeySpec &bk,
+                     Bucketed *out) {
+  memset(out, 0, sizeof *out);
+  out->key = bk;
+  out->n_buckets = (uint32_t)(bk.dead >> LSG_BUCKET_SHIFT);
+  SpanBucketFn fn{idents, (uint32_t)n_idents, bk, out->n_buckets};
+  return bucket_partition(ctx, spans, n, fn, out->n_buckets + 1, nullptr, WS_BK_SP, WS_BK_SP_ORIG, WS_BK_SP_ENDS, WS_SPAN_HIST, WS_SPAN_KEYS_A, PK_BK_SPANS,
+                          PK_BK_SPANS, out);
+}
+
 // ---- F1 support: the events of one signal in stable (pod, exact time) order ---------------------------------
 namespace {
 struct PodStats { long long ts_min, ts_max; unsigned long long n_live; unsigned int max_pod, bad; unsigned int pad[2]; };
