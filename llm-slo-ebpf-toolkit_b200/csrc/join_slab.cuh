@@ -184,6 +184,7 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
   const JoinParams &jp = p.j;
   if (tid < 5) sm.cnt[tid] = 0;
+  __syncthreads();
   unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
   const uint64_t W = (uint64_t)jp.window_ns;
   const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
@@ -192,89 +193,77 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
   const uint32_t gmask = (1u << p.gshift) - 1u, nbk = p.n_buckets;
   const uint32_t shift = p.ks.shift;
   const uint32_t n_tiles = *p.n_tiles;
-  uint32_t bc_next = 0, b1_cur = 0;      // thread 0's cursor inside the current tile
+  uint32_t t_cur = blockIdx.x, bc_next = 0, b1_cur = 0;   // the CTA's tile (strided over the list) and the cursor inside it
   bool have_tile = false;
 
   for (;;) {
-    // ---- next unit: warp 0 cuts the current tile (or takes the next one) into what fits shared memory
-    __syncthreads();
-    if (warp == 0) {
-      uint32_t kind = JS_UNIT_DONE, bc = 0, be = 0, lo = 0, hi = 0, S0 = 0, nS = 0;
-      for (;;) {
-        if (!have_tile) {
-          uint32_t t = 0;
-          if (lane == 0) t = atomicAdd(p.next_tile, 1u);
-          t = __shfl_sync(0xffffffffu, t, 0);
-          if (t >= n_tiles) break;
-          const uint2 tb = p.tiles[t];
-          if (tb.x == nbk) {   // a chunk of the spans that can match nothing
-            kind = JS_UNIT_DEAD;
-            S0 = bk_start(p.sp_ends, nbk) + tb.y * JS_CH;
-            nS = min((uint32_t)JS_CH, bk_start(p.sp_ends, nbk + 1) - S0);
-            bc = be = lo = hi = nbk;
-            break;
-          }
-          bc_next = tb.x; b1_cur = tb.y; have_tile = true;
-          // the next tile's events are wanted soon: ask L2 for the first part of the piece now
+    // ---- next unit: the current tile (or the next one) is cut into what fits shared memory.  Every warp does the same
+    //      cut from the same (L2-resident) bucket tables, so nothing has to be exchanged and nobody waits for warp 0.
+    uint32_t kind = JS_UNIT_DONE, bc = 0, be = 0, lo_b = 0, hi_b = 0, S0 = 0, nS = 0;
+    for (;;) {
+      if (!have_tile) {
+        if (t_cur >= n_tiles) break;
+        const uint2 tb = __ldg(p.tiles + t_cur);
+        t_cur += gridDim.x;
+        if (tb.x == nbk) {   // a chunk of the spans that can match nothing
+          kind = JS_UNIT_DEAD;
+          S0 = bk_start(p.sp_ends, nbk) + tb.y * JS_CH;
+          nS = min((uint32_t)JS_CH, bk_start(p.sp_ends, nbk + 1) - S0);
+          bc = be = lo_b = hi_b = nbk;
+          break;
         }
-        // first bucket at or after bc_next that holds spans
-        uint32_t b = bc_next;
-        while (b < b1_cur) {
-          const uint32_t bb = b + lane;
-          const bool has = bb < b1_cur && bk_start(p.sp_ends, bb + 1) > bk_start(p.sp_ends, bb);
-          const unsigned m = __ballot_sync(0xffffffffu, has);
-          if (m) { b += __ffs(m) - 1; break; }
-          b += 32;
-        }
-        if (b >= b1_cur) { have_tile = false; continue; }
-        bc = b;
-        const uint32_t glo = bc & ~gmask, ghi = glo + gmask + 1u;
-        const uint32_t gend = b1_cur < ghi ? b1_cur : ghi;
-        lo = bc > glo ? bc - 1 : bc;
-        // lane m proposes the core [bc, bc + m + 1): it fits when the loaded buckets [lo, hi) are at most JS_MAXB and
-        // hold at most `cap` events
-        const uint32_t e_lo = bk_start(p.ev_ends, lo);
-        const uint32_t cand_be = bc + lane + 1;
-        bool fits = false;
-        if (cand_be <= gend) {
-          const uint32_t h = cand_be + 1 < ghi ? cand_be + 1 : ghi;
-          fits = h - lo <= (uint32_t)JS_MAXB && bk_start(p.ev_ends, h) - e_lo <= cap;
-        }
-        const unsigned fm = __ballot_sync(0xffffffffu, fits);
-        const int n_fit = __ffs(~fm) - 1;   // conditions are monotone: the leading run of ones (32 lanes > JS_MAXB)
-        if (n_fit <= 0) {
-          kind = JS_UNIT_BIG;   // this bucket with its halos is larger than a tile
-          be = bc + 1;
-        } else {
-          kind = JS_UNIT_TILE;
-          be = bc + (uint32_t)n_fit;
-        }
-        hi = be + 1 < ghi ? be + 1 : ghi;
-        bc_next = be;
-        S0 = bk_start(p.sp_ends, bc);
-        nS = bk_start(p.sp_ends, be) - S0;
-        break;
+        bc_next = tb.x; b1_cur = tb.y; have_tile = true;
       }
-      if (lane == 0) {
-        sm.u_kind = kind; sm.u_bc = bc; sm.u_be = be; sm.u_lo = lo; sm.u_hi = hi; sm.u_S0 = S0; sm.u_nS = nS;
-        const uint32_t E0 = kind == JS_UNIT_TILE ? bk_start(p.ev_ends, lo) : 0u;
-        sm.u_E0 = E0;
-        sm.u_nE = kind == JS_UNIT_TILE ? bk_start(p.ev_ends, hi) - E0 : 0u;
-        sm.cls_min = 0xffffffffu; sm.cls_max = 0u;
+      // first bucket at or after bc_next that holds spans
+      uint32_t b = bc_next;
+      while (b < b1_cur) {
+        const uint32_t bb = b + lane;
+        const bool has = bb < b1_cur && bk_start(p.sp_ends, bb + 1) > bk_start(p.sp_ends, bb);
+        const unsigned m = __ballot_sync(0xffffffffu, has);
+        if (m) { b += __ffs(m) - 1; break; }
+        b += 32;
       }
+      if (b >= b1_cur) { have_tile = false; continue; }
+      bc = b;
+      const uint32_t glo = bc & ~gmask, ghi = glo + gmask + 1u;
+      const uint32_t gend = b1_cur < ghi ? b1_cur : ghi;
+      lo_b = bc > glo ? bc - 1 : bc;
+      // lane m proposes the core [bc, bc + m + 1): it fits when the loaded buckets [lo, hi) are at most JS_MAXB and
+      // hold at most `cap` events
+      const uint32_t e_lo = bk_start(p.ev_ends, lo_b);
+      const uint32_t cand_be = bc + lane + 1;
+      bool fits = false;
+      if (cand_be <= gend) {
+        const uint32_t h = cand_be + 1 < ghi ? cand_be + 1 : ghi;
+        fits = h - lo_b <= (uint32_t)JS_MAXB && bk_start(p.ev_ends, h) - e_lo <= cap;
+      }
+      const unsigned fm = __ballot_sync(0xffffffffu, fits);
+      const int n_fit = __ffs(~fm) - 1;   // conditions are monotone: the leading run of ones (32 lanes > JS_MAXB)
+      if (n_fit <= 0) {
+        kind = JS_UNIT_BIG;   // this bucket with its halos is larger than a tile
+        be = bc + 1;
+      } else {
+        kind = JS_UNIT_TILE;
+        be = bc + (uint32_t)n_fit;
+      }
+      hi_b = be + 1 < ghi ? be + 1 : ghi;
+      bc_next = be;
+      S0 = bk_start(p.sp_ends, bc);
+      nS = bk_start(p.sp_ends, be) - S0;
+      break;
     }
-    __syncthreads();
-    const uint32_t kind = sm.u_kind;
     if (kind == JS_UNIT_DONE) break;
-    const uint32_t S0 = sm.u_S0, nS = sm.u_nS;
     if (kind == JS_UNIT_BIG) {
       // every span of the bucket goes to the warp-per-span kernel
       for (uint32_t k = tid; k < nS; k += JS_THREADS) big_list[atomicAdd(big_count, 1u)] = S0 + k;
       continue;
     }
-    const uint32_t E0 = sm.u_E0, nE = sm.u_nE, lo_b = sm.u_lo;
-    const uint32_t nq = (sm.u_hi - lo_b) << LSG_BUCKET_SHIFT;        // time quanta of the loaded buckets (0 for dead spans)
+    const uint32_t E0 = kind == JS_UNIT_TILE ? bk_start(p.ev_ends, lo_b) : 0u;
+    const uint32_t nE = kind == JS_UNIT_TILE ? bk_start(p.ev_ends, hi_b) - E0 : 0u;
+    const uint32_t nq = (hi_b - lo_b) << LSG_BUCKET_SHIFT;             // time quanta of the loaded buckets (0 for dead spans)
     const uint64_t q0 = (uint64_t)(lo_b & gmask) << LSG_BUCKET_SHIFT;   // the tile's first quantum on the group's time axis
+    __syncthreads();   // the previous unit's last sub-chunk is done with the tables that are rebuilt now
+    if (tid == 0) { sm.cls_min = 0xffffffffu; sm.cls_max = 0u; }
 
     // ---- stage A: quantum and rank of every event
     for (uint32_t q = tid; q < nq + 1; q += JS_THREADS) sm.qs[q] = 0;
@@ -372,14 +361,14 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
           wo = pos_of(((off + Wi) >> shift) + 1);
           const uint64_t qa = off > Wi ? (off - Wi + quantum - 1) >> shift : 0;   // first quantum starting at or after ts - Wi
           const uint64_t qb1 = (off + Wi + 1) >> shift;                             // first quantum not ending by ts + Wi
+          z2 = max(zo, min(wo, pos_of(off > W2 ? (off - W2) >> shift : 0)));
+          w2 = max(z2, min(wo, pos_of(((off + W2) >> shift) + 1)));
           if (qa < qb1) {
             x1 = max(zo, min(wo, pos_of(qa)));
             y1 = max(x1, min(wo, pos_of(qb1)));
           } else {
-            x1 = y1 = wo;
+            x1 = y1 = z2;   // no whole quantum inside the window (a quantum wider than it): everything is enumerated
           }
-          z2 = max(zo, min(wo, pos_of(off > W2 ? (off - W2) >> shift : 0)));
-          w2 = max(z2, min(wo, pos_of(((off + W2) >> shift) + 1)));
         }
         sm.r_ox[tid] = ox; sm.r_oy[tid] = oy; sm.r_zo[tid] = zo; sm.r_wo[tid] = wo;
         sm.r_x1[tid] = x1; sm.r_y1[tid] = y1; sm.r_z2[tid] = z2; sm.r_w2[tid] = w2;
@@ -404,32 +393,9 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
             old = atomicCAS(hp, assumed, (unsigned short)tid);
           } while (old != assumed);
         }
-        // pairs this span contributes to the flattened list
-        uint32_t len;
-        if (counted) {
-          const uint32_t zo = sm.r_zo[tid], wo = sm.r_wo[tid], x1 = sm.r_x1[tid], y1 = sm.r_y1[tid], z2 = sm.r_z2[tid], w2 = sm.r_w2[tid];
-          len = (min(x1, z2) - zo) + (w2 - z2) + (wo - max(y1, w2));
-        } else {
-          len = sm.r_wo[tid] - sm.r_zo[tid];
-        }
-        sm.P[tid + 1] = len;
       }
-      if (tid == 0) sm.P[0] = 0;
       __syncthreads();
-      // ---- prefix of the pair counts (warp 0), then tier 1: every staged event probes the hash once
-      if (warp == 0) {
-        uint32_t v[4], t = 0;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { const int k = (int)lane * 4 + u; v[u] = k < ns ? sm.P[k + 1] : 0u; t += v[u]; }
-        uint32_t x = t;
-        for (int o = 1; o < 32; o <<= 1) {
-          const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-          if (lane >= (unsigned)o) x += y;
-        }
-        uint32_t run = x - t;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { const int k = (int)lane * 4 + u; run += v[u]; if (k < ns) sm.P[k + 1] = run; }
-      }
+      // ---- tier 1: every staged event probes the hash once
       for (uint32_t o = tid; o < nE; o += JS_THREADS) {
         const uint32_t tr = trs[o] >> 4;
         if (tr == 0) continue;
@@ -457,101 +423,86 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
         }
       }
       __syncthreads();
-      // ---- tiers 2-4: the sub-chunk's pairs end to end, an equal slice per thread
+      // ---- tiers 2-4: one warp per span, the lanes stride over the span's pairs.  Span data is warp-uniform, every
+      //      count is a ballot, and notes are appended at ballot ranks (no atomics, no per-lane loop state).
       {
-        const uint32_t Pt = sm.P[ns];
-        const uint32_t per = (Pt + JS_THREADS - 1) / JS_THREADS;
-        uint32_t j = min(tid * per, Pt);
-        const uint32_t jend = min(j + per, Pt);
-        if (j < jend) {
-          int k;
-          {
-            int a = 0, b = ns;   // P[a] <= j < P[b]
-            while (b - a > 1) {
-              const int mid = (a + b) >> 1;
-              if (sm.P[mid] <= j) a = mid; else b = mid;
-            }
-            k = a;
+        const uint32_t Wi32 = (uint32_t)Wi;
+        for (int k = (int)warp; k < ns; k += JS_THREADS / 32) {
+          const SpanRec s = span_from_halves(sm.span[k][0], sm.span[k][1]);
+          const uint32_t zo = sm.r_zo[k], wo = sm.r_wo[k];
+          if (zo >= wo) continue;   // nothing inside the inner window (also: every span that can match nothing)
+          const uint2 spc = __ldg(jp.ident_pc + s.ident);
+          const bool pod_ok = spc.x != 0, pid_ok = s.pid != 0, conn_ok = s.conn != 0;
+          const uint32_t s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
+          const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
+          const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;
+          const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)jp.fanout;   // the kept list is already full of trace-id matches
+          const uint32_t x1 = sm.r_x1[k], y1 = sm.r_y1[k];
+          // segments that are enumerated: everything but the quanta wholly inside the window that lie outside +-250 ms
+          uint32_t a0 = zo, lenA = wo - zo, b0 = 0, lenB = 0, c0s = 0, lenC = 0;
+          if (counted) {
+            const uint32_t z2 = sm.r_z2[k], w2 = sm.r_w2[k];
+            lenA = min(x1, z2) - zo;
+            b0 = z2; lenB = w2 - z2;
+            c0s = max(y1, w2); lenC = wo - c0s;
           }
-          while (j < jend) {
-            const uint32_t pk1 = sm.P[k + 1];
-            if (pk1 <= j) { ++k; continue; }   // spans without pairs
-            uint32_t take = min(jend, pk1) - j;
-            uint32_t off = j - sm.P[k];
-            j += take;
-            const SpanRec s = span_from_halves(sm.span[k][0], sm.span[k][1]);
-            const uint2 spc = __ldg(jp.ident_pc + s.ident);
-            const bool pod_ok = spc.x != 0, pid_ok = s.pid != 0, conn_ok = s.conn != 0;
-            const uint32_t s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
-            const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
-            const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;
-            const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)jp.fanout;   // the kept list is already full of trace-id matches
-            const uint32_t x1 = sm.r_x1[k], y1 = sm.r_y1[k];
-            uint32_t seg_b[3], seg_e[3];
-            if (counted) {
-              const uint32_t zo = sm.r_zo[k], wo = sm.r_wo[k], z2 = sm.r_z2[k], w2 = sm.r_w2[k];
-              seg_b[0] = zo; seg_e[0] = min(x1, z2);
-              seg_b[1] = z2; seg_e[1] = w2;
-              seg_b[2] = max(y1, w2); seg_e[2] = wo;
+          const uint32_t lenAB = lenA + lenB, total = lenAB + lenC;
+          uint32_t n_note = sm.n_note[k];          // the probe's trace-id notes come first
+          uint32_t n_match = 0, n_low = 0, n_edge = 0, n_23 = 0, n_unl = 0;   // warp-uniform
+          for (uint32_t jb = 0; jb < total; jb += 32) {
+            const uint32_t j = jb + lane;
+            const bool valid = j < total;
+            const uint32_t o = j < lenA ? a0 + j : (j < lenAB ? b0 + (j - lenA) : c0s + (j - lenAB));
+            uint4 e = make_uint4(0, 0, 0, 0);
+            uint32_t e_tr = 0;
+            if (valid) { e = q4[o]; e_tr = trs[o] >> 4; }
+            bool in, in100, in250;
+            if (T32) {
+              const int32_t d = (int32_t)(e.x - s_lo);
+              const uint32_t ad = (uint32_t)(d < 0 ? -d : d);
+              in = ad <= Wi32; in100 = ad <= (uint32_t)(100 * kMs); in250 = ad <= (uint32_t)(250 * kMs);
             } else {
-              seg_b[0] = sm.r_zo[k]; seg_e[0] = sm.r_wo[k];
-              seg_b[1] = seg_e[1] = seg_b[2] = seg_e[2] = 0;
+              const uint64_t ad = valid ? lsg_absdiff(s.ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | e.x)) : ~0ull;
+              in = ad <= Wi; in100 = ad <= (uint64_t)(100 * kMs); in250 = ad <= (uint64_t)(250 * kMs);
             }
-            uint32_t n_match = 0, n_low = 0, n_edge = 0, n_23 = 0, n_unl = 0;
-#pragma unroll
-            for (int sg = 0; sg < 3; ++sg) {
-              const uint32_t len = seg_e[sg] - seg_b[sg];
-              if (off >= len) { off -= len; continue; }
-              const uint32_t ob = seg_b[sg] + off;
-              const uint32_t cnt = min(len - off, take);
-              off = 0;
-              take -= cnt;
-              for (uint32_t o = ob; o < ob + cnt; ++o) {
-                const uint4 e = q4[o];
-                const uint32_t e_tr = trs[o] >> 4;
-                uint64_t ad;
-                if (T32) {
-                  const int32_t d = (int32_t)(e.x - s_lo);
-                  ad = (uint64_t)(uint32_t)(d < 0 ? -d : d);
-                } else {
-                  ad = lsg_absdiff(s.ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | e.x));
-                }
-                const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
-                const bool same_pod = pod_ok & (e.y == spc.x);
-                const bool t2 = same_pod & pid_ok & (e.z == s.pid) & in100;        // dns.go:61-64
-                const bool t3 = same_pod & conn_ok & (e.w == s.conn) & in250;      // dns.go:65-68
-                int tier;
-                bool m;
-                if (counted) {
-                  tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
-                  m = in & (e_tr != no_trace) & (t2 | t3);
-                  n_23 += m;
-                  n_edge += in & ((o < x1) | (o >= y1));
-                } else {
-                  const bool same_sn = cls[o] == s_cls;
-                  tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
-                  m = in & (e_tr != no_trace) & (tier != 0);
-                }
-                n_match += m;
-                const bool low = m & (tier > cut);                                 // correlator.go:83-86
-                n_low += low;
+            in &= valid;
+            const bool same_pod = pod_ok & (e.y == spc.x);
+            const bool t2 = same_pod & pid_ok & (e.z == s.pid) & in100;        // dns.go:61-64
+            const bool t3 = same_pod & conn_ok & (e.w == s.conn) & in250;      // dns.go:65-68
+            int tier;
+            bool m;
+            if (counted) {
+              tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
+              m = in & (e_tr != no_trace) & (t2 | t3);
+              n_23 += __popc(__ballot_sync(0xffffffffu, m));
+              n_edge += __popc(__ballot_sync(0xffffffffu, in & ((o < x1) | (o >= y1))));
+            } else {
+              const bool same_sn = valid && cls[o] == s_cls;
+              tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
+              m = in & (e_tr != no_trace) & (tier != 0);
+            }
+            const unsigned mm = __ballot_sync(0xffffffffu, m);
+            if (mm == 0) continue;
+            n_match += __popc(mm);
+            const bool low = m & (tier > cut);                                 // correlator.go:83-86
+            const unsigned lm = __ballot_sync(0xffffffffu, low);
+            n_low += __popc(lm);
+            const unsigned cm = mm & ~lm;                                      // candidates
+            if (cm) {
+              if (full) {
+                n_unl += __popc(cm);
+              } else {
                 if (m & !low) {
-                  if (full) {
-                    n_unl++;
-                  } else {
-                    const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-                    if (at < JS_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
-                  }
+                  const uint32_t at = n_note + __popc(cm & ((1u << lane) - 1u));
+                  if (at < JS_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
                 }
+                n_note += __popc(cm);
               }
-              if (take == 0) break;
             }
-            if (n_match) atomicAdd(&sm.n_match[k], n_match);
-            if (n_low) atomicAdd(&sm.n_low[k], n_low);
-            if (n_edge) atomicAdd(&sm.n_edge[k], n_edge);
-            if (n_23) atomicAdd(&sm.n_23[k], n_23);
-            if (n_unl) atomicAdd(&sm.n_unl[k], n_unl);
-            ++k;
+          }
+          if (lane == 0) {
+            sm.n_note[k] = n_note; sm.n_match[k] = n_match; sm.n_low[k] = n_low; sm.n_edge[k] = n_edge; sm.n_23[k] = n_23;
+            sm.n_unl[k] = n_unl;
           }
         }
       }
@@ -572,18 +523,29 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
           n_cand = sm.n_note[k];
           redo = n_cand > (uint32_t)JS_LIST;
           if (!redo) {
-#pragma unroll 2
-            for (uint32_t i = h; i < n_cand; i += 2) {
-              const uint32_t e = sm.note[i][k];
-              const uint32_t o = e & 0xfffu, tier = e >> 12;
-              uint64_t adt;
-              if (T32) {   // a noted candidate is within the window of its span
-                const int32_t d = (int32_t)(q4[o].x - (uint32_t)(uint64_t)s.ts);
-                adt = (uint64_t)(uint32_t)(d < 0 ? -d : d);
-              } else {
-                adt = lsg_absdiff(s.ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | q4[o].x));
+            // four notes at a time: their input indices (the tie-break of the reference's stable sort) are global loads,
+            // issued together so that their latency is paid once per batch
+            for (uint32_t i = h; i < n_cand; i += 8) {
+              uint32_t ent[4], orig[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const uint32_t ix = i + 2 * u;
+                ent[u] = ix < n_cand ? (uint32_t)sm.note[ix][k] : 0xffffffffu;
+                orig[u] = ent[u] != 0xffffffffu ? __ldg(p.ev_orig + E0 + slot[ent[u] & 0xfffu]) : 0u;
               }
-              top.insert(((uint64_t)tier << 56) | adt, __ldg(p.ev_orig + E0 + slot[o]), o);
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                if (ent[u] == 0xffffffffu) continue;
+                const uint32_t o = ent[u] & 0xfffu, tier = ent[u] >> 12;
+                uint64_t adt;
+                if (T32) {   // a noted candidate is within the window of its span
+                  const int32_t d = (int32_t)(q4[o].x - (uint32_t)(uint64_t)s.ts);
+                  adt = (uint64_t)(uint32_t)(d < 0 ? -d : d);
+                } else {
+                  adt = lsg_absdiff(s.ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | q4[o].x));
+                }
+                top.insert(((uint64_t)tier << 56) | adt, orig[u], o);
+              }
             }
           }
         }

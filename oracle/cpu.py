@@ -44,6 +44,10 @@ def lib():
         L.orc_segment_quantiles.restype = None
         L.orc_retry_storm.restype = None
         L.orc_hw_threads.restype = cint
+        L.orc_synth_n_incidents.argtypes = [C.POINTER(A.SynthCfg)]
+        L.orc_synth_n_incidents.restype = sz
+        L.orc_synth_range.argtypes = [C.POINTER(A.SynthCfg), C.c_uint64, C.c_uint64, vp, C.c_uint64, C.c_uint64, vp, vp, vp, vp,
+                                      vp, cint]
         _LIB = L
     return _LIB
 
@@ -135,3 +139,19 @@ def segment_quantiles(values, segment, n_segments, q):
 
 def hw_threads():
     return lib().orc_hw_threads()
+
+
+def generate_host(cfg, nthreads=0):
+    """The synthetic workload of csrc/synth_common.h generated by the host-only copy inside liboracle.so (same header,
+    same bytes as lsg_synth_host / lsg_synth_dev), so that a caller need not map the product library."""
+    L = lib()
+    n_inc = L.orc_synth_n_incidents(C.byref(cfg))
+    out = {"spans": np.zeros(cfg.n_spans, A.SPAN_DTYPE), "events": np.zeros(cfg.n_events, A.EVENT_DTYPE),
+           "idents": np.zeros(cfg.n_pods, A.IDENT_DTYPE), "inc_actual": np.zeros(n_inc, np.uint8),
+           "inc_expected": np.zeros(n_inc, np.uint32), "inc_expected_n": np.zeros(n_inc, np.uint8)}
+    rc = L.orc_synth_range(C.byref(cfg), 0, cfg.n_spans, _p(out["spans"]), 0, cfg.n_events, _p(out["events"]), _p(out["idents"]),
+                           _p(out["inc_actual"]), _p(out["inc_expected"]), _p(out["inc_expected_n"]),
+                           int(nthreads) if nthreads > 0 else max(1, hw_threads()))
+    if rc != 0:
+        raise ValueError("invalid synthetic workload configuration")
+    return out
