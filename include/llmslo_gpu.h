@@ -143,6 +143,11 @@ const char *lsg_last_error(const lsg_ctx *ctx);
 const char *lsg_version(void);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t lsg_launch_count(const lsg_ctx *ctx);
+/* Which of the two implementations of the sort + join stages lsg_process_batch / lsg_pipeline take (same results):
+ * 0 = permutation sort (counting / radix) + a join that gathers its tiles through the permutation (default),
+ * 1 = bucket partition of the records + slab join on contiguous tiles, -1 = the LSG_JOIN_PATH environment variable
+ * ("slab" or "perm") decides.  A tuning knob with no reference counterpart. */
+int lsg_set_join_path(lsg_ctx *ctx, int path);
 /* bytes of device workspace currently held */
 size_t lsg_workspace_bytes(const lsg_ctx *ctx);
 

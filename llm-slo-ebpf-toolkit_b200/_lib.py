@@ -47,6 +47,7 @@ def load_library():
         lib.lsg_version.restype = C.c_char_p
         lib.lsg_launch_count.argtypes = [vp]
         lib.lsg_launch_count.restype = C.c_uint64
+        lib.lsg_set_join_path.argtypes = [vp, cint]
         lib.lsg_workspace_bytes.argtypes = [vp]
         lib.lsg_workspace_bytes.restype = sz
         lib.lsg_default_model.argtypes = [P(A.Model)]
@@ -258,6 +259,10 @@ class Context:
         b, sh, ps = C.c_uint32(), C.c_uint32(), C.c_uint32()
         self._check(self._lib.lsg_last_sort_info(self._h, C.byref(b), C.byref(sh), C.byref(ps)))
         return {"key_bits": b.value, "time_shift": sh.value, "passes": ps.value}
+
+    def set_join_path(self, path):
+        """0: permutation sort + gathering join (default), 1: bucket partition + slab join, -1: LSG_JOIN_PATH decides."""
+        self._check(self._lib.lsg_set_join_path(self._h, int(path)))
 
     def profile_enable(self, on=True):
         self._check(self._lib.lsg_profile_enable(self._h, 1 if on else 0))

@@ -143,3 +143,105 @@ def WriteEvalSummary(path, report, generated_at=None):
 
 def WriteConfusionCSV(path, matrix):
     _write(path, ConfusionCSV(matrix))
+
+
+# ---- cmd/attributor's attributions.jsonl and pkg/benchmark's harness artifacts ---------------------------------------
+def _go_json_compact(obj) -> str:
+    """json.Marshal / json.Encoder.Encode without indentation: struct field order, Go float formatting, HTML-safe
+    escaping of <, > and & as encoding/json does by default."""
+    if isinstance(obj, dict):
+        return "{" + ",".join("%s:%s" % (_go_json_compact(str(k)), _go_json_compact(v)) for k, v in obj.items()) + "}"
+    if isinstance(obj, (list, tuple)):
+        return "[" + ",".join(_go_json_compact(v) for v in obj) + "]"
+    if isinstance(obj, bool):
+        return "true" if obj else "false"
+    if isinstance(obj, int):
+        return str(obj)
+    if isinstance(obj, float):
+        return go_float(obj)
+    if obj is None:
+        return "null"
+    return json.dumps(obj, ensure_ascii=False).replace("<", "\\u003c").replace(">", "\\u003e").replace("&", "\\u0026")
+
+
+def _rfc3339(ts) -> str:
+    """time.Time.Format(time.RFC3339) of a sample timestamp given as an RFC3339 string (fractions are dropped, as
+    RFC3339 without Nano does) or None / empty for Go's zero Time."""
+    if not ts:
+        return "0001-01-01T00:00:00Z"
+    return ts.split(".")[0] + ("Z" if "." in ts and not ts.split(".")[0].endswith("Z") else "")
+
+
+def _rfc3339_minus(ts, seconds) -> str:
+    if not ts:
+        # zero Time minus 30 s: year 0, which Go prints as 0000-12-31T23:59:30Z
+        return "0000-12-31T23:59:%02dZ" % (60 - seconds)
+    from datetime import timedelta
+    base = datetime.strptime(_rfc3339(ts), "%Y-%m-%dT%H:%M:%SZ").replace(tzinfo=timezone.utc)
+    return (base - timedelta(seconds=seconds)).strftime("%Y-%m-%dT%H:%M:%SZ")
+
+
+def _json_time(ts) -> str:
+    """time.Time's MarshalJSON (RFC3339Nano: trailing zeros of the fraction dropped)."""
+    if not ts:
+        return "0001-01-01T00:00:00Z"
+    if "." in ts:
+        head, frac = ts.rstrip("Z").split(".")
+        frac = frac.rstrip("0")
+        return head + ("." + frac if frac else "") + "Z"
+    return ts
+
+
+def AttributionsJSONL(predictions) -> str:
+    """cmd/attributor/main.go:203-224: one json.Encoder.Encode(schema.IncidentAttribution) per line
+    (pkg/schema/types.go:20-57 field order and omitempty rules)."""
+    lines = []
+    for p in predictions:
+        d = {"incident_id": p.IncidentID, "timestamp": _json_time(p.Timestamp), "cluster": p.Cluster}
+        if p.Namespace:
+            d["namespace"] = p.Namespace
+        d["service"] = p.Service
+        d["predicted_fault_domain"] = p.PredictedFaultDomain
+        d["confidence"] = float(p.Confidence)
+        d["evidence"] = [{"signal": e["signal"], "value": float(e["value"]) if isinstance(e["value"], (int, float)) and
+                          not isinstance(e["value"], bool) else e["value"], "source": e["source"]} for e in p.Evidence]
+        d["slo_impact"] = {"sli": p.SLOImpact.get("sli", ""), "burn_rate": float(p.SLOImpact.get("burn_rate", 0.0)),
+                           "window_minutes": int(p.SLOImpact.get("window_minutes", 0))}
+        if p.TraceIDs:
+            d["trace_ids"] = list(p.TraceIDs)
+        if p.RequestIDs:
+            d["request_ids"] = list(p.RequestIDs)
+        if p.FaultHypotheses:
+            d["fault_hypotheses"] = [{"domain": h.Domain, "posterior": float(h.Posterior), "evidence": list(h.Evidence)}
+                                     for h in p.FaultHypotheses]
+        lines.append(_go_json_compact(d) + "\n")
+    return "".join(lines)
+
+
+def IncidentPredictionsCSV(scenario, samples, predictions, map_fault_label) -> str:
+    """pkg/benchmark/harness.go:285-343 (writeIncidentPredictions): "%.2f" confidence, the constant 2.5 s delay."""
+    rows = [["timestamp", "incident_id", "scenario", "fault_start_ts", "fault_end_ts", "predicted_fault_domain",
+             "ground_truth_fault_domain", "confidence", "detection_delay_seconds", "is_correct"]]
+    for sample, pred in zip(samples, predictions):
+        actual = sample.ExpectedDomain or map_fault_label(sample.FaultLabel)
+        rows.append([_rfc3339(sample.Timestamp), sample.IncidentID, scenario, _rfc3339_minus(sample.Timestamp, 30),
+                     _rfc3339(sample.Timestamp), pred.PredictedFaultDomain, actual, "%.2f" % pred.Confidence, "2.5",
+                     _bool(pred.PredictedFaultDomain == actual)])
+    return _csv(rows)
+
+
+def HarnessConfusionCSV(matrix) -> str:
+    """pkg/benchmark/harness.go:345-377 (writeConfusionMatrix): the same rows as cmd/attributor's confusion.csv."""
+    return ConfusionCSV(matrix)
+
+
+def WriteAttributionsJSONL(path, predictions):
+    _write(path, AttributionsJSONL(predictions))
+
+
+def WriteIncidentPredictions(path, scenario, samples, predictions, map_fault_label):
+    _write(path, IncidentPredictionsCSV(scenario, samples, predictions, map_fault_label))
+
+
+def WriteAttributorSummary(path, *args, **kw):
+    _write(path, AttributorSummaryJSON(*args, **kw))

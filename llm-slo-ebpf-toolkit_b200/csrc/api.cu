@@ -119,12 +119,14 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans, hint));
   void *small_v;
   LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
-  // Default path: the records are moved once into (group, time slab) buckets and the slab join stages contiguous
-  // tiles (sort.cu "bucket partition", join_slab.cuh).  LSG_JOIN_PATH=perm keeps the permutation sort + gathering join
-  // (also taken when the bucket tables would be out of proportion to the batch).
+  // Two ways from here.  Default: permutation sort + the join that gathers its own tiles (the faster one as measured,
+  // profiles/r02_*).  The other: the records are moved once into (group, time slab) buckets and the slab join stages
+  // contiguous tiles (sort.cu "bucket partition", join_slab.cuh): DRAM traffic close to the algorithmic bytes, but the
+  // in-tile counting sort and its barriers cost more than the gather's latency.  lsg_set_join_path / LSG_JOIN_PATH=slab.
   static const char *path_env = getenv("LSG_JOIN_PATH");
+  const bool want_slab = ctx->join_path == 1 || (ctx->join_path < 0 && path_env && strcmp(path_env, "slab") == 0);
   const KeySpec bk = lsg_bucket_keyspec(sorted->key, n_events, window_ns);
-  if (!(path_env && strcmp(path_env, "perm") == 0) && lsg_bucket_path_ok(bk, n_events, n_spans, window_ns, fanout)) {
+  if (want_slab && lsg_bucket_path_ok(bk, n_events, n_spans, window_ns, fanout)) {
     Bucketed bev, bsp;
     const uint2 *ident_pc = nullptr;
     {
@@ -344,6 +346,11 @@ int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_sh
 }
 
 const char *lsg_last_error(const lsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+int lsg_set_join_path(lsg_ctx *ctx, int path) {
+  if (!ctx || path < -1 || path > 1) return LSG_ERR_INVALID;
+  ctx->join_path = path;
+  return 0;
+}
 uint64_t lsg_launch_count(const lsg_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int lsg_host_alloc(size_t bytes, int write_combined, void **out) {
   if (!out) return LSG_ERR_INVALID;

@@ -132,6 +132,7 @@ struct lsg_ctx {
   DevModel model;
   bool model_set = false;
   KeySpec last_key = {};   // key layout of the most recent event sort (diagnostics)
+  int join_path = -1;      // -1: LSG_JOIN_PATH decides (default perm), 0: permutation sort + gathering join, 1: bucket partition + slab join
 };
 
 int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...);

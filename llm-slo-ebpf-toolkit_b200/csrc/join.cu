@@ -37,6 +37,7 @@
 // accumulated from the epilogue with one atomicMax per present attribute.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -1122,7 +1123,9 @@ int lsg_launch_join_slab(lsg_ctx *ctx, const JoinArgs &a, const Bucketed &ev, co
   LSG_CUDA(ctx, cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, ctx->device));
   LSG_CUDA(ctx, cudaDeviceGetAttribute(&dev_resv, cudaDevAttrReservedSharedMemoryPerBlock, ctx->device));
   const size_t fixed = (sizeof(SlabFixed) + 15) & ~(size_t)15;
-  size_t budget = (size_t)dev_smem / 2 - (size_t)dev_resv - 256;
+  static const int occ_want = getenv("LSG_SLAB_OCC") ? atoi(getenv("LSG_SLAB_OCC")) : 3;   // CTAs per SM (2 or 3): 3 measured 15 % faster on C2
+  const int occ_t = occ_want == 2 || a.fanout > 3 ? 2 : 3;
+  size_t budget = (size_t)dev_smem / occ_t - (size_t)dev_resv - 256;
   uint32_t cap = (uint32_t)((budget - fixed) / slab_bytes_per_event(t32));
   if (cap > 4088) cap = 4088;   // a note keeps the tile position in 12 bits
   cap &= ~7u;
@@ -1137,9 +1140,10 @@ int lsg_launch_join_slab(lsg_ctx *ctx, const JoinArgs &a, const Bucketed &ev, co
     return 0;
   };
   if (a.fanout <= 3) {
-    if (t32) LSG_TRY(launch(k_join_slab<3, true>)); else LSG_TRY(launch(k_join_slab<3, false>));
+    if (occ_t == 3) { if (t32) LSG_TRY(launch(k_join_slab<3, true, 3>)); else LSG_TRY(launch(k_join_slab<3, false, 3>)); }
+    else { if (t32) LSG_TRY(launch(k_join_slab<3, true, 2>)); else LSG_TRY(launch(k_join_slab<3, false, 2>)); }
   } else if (a.fanout <= TM_MAX_F) {
-    if (t32) LSG_TRY(launch(k_join_slab<TM_MAX_F, true>)); else LSG_TRY(launch(k_join_slab<TM_MAX_F, false>));
+    if (t32) LSG_TRY(launch(k_join_slab<TM_MAX_F, true, 2>)); else LSG_TRY(launch(k_join_slab<TM_MAX_F, false, 2>));
   } else {
     // more kept candidates than the tile kernel holds in registers: every span goes to the warp-per-span kernel
     k_list_bucketed_spans<<<(unsigned)std::min<size_t>((a.n_spans + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(

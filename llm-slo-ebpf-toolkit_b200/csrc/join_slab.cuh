@@ -22,7 +22,7 @@
 // Spans that do not fit (a bucket with its halos larger than a tile, more notes than the list holds, fanout > 8) go
 // to k_join_big_slab: one warp per span over its three buckets straight from global memory.
 
-constexpr int JS_THREADS = 256;
+constexpr int JS_THREADS = 256;   // (512 threads x 2 CTAs measured the same as 256 x 2; 256 x 3 with smaller tiles is the fastest)
 constexpr int JS_CH = 128;        // spans per sub-chunk
 constexpr int JS_LIST = 32;       // noted candidates per span
 constexpr int JS_QCAP = 1024;     // time quanta per tile: 16 buckets
@@ -146,11 +146,9 @@ k_join_big_slab(const __grid_constant__ SlabParams p, const uint32_t *__restrict
 struct SlabFixed {
   uint4 span[JS_CH][2];
   uint32_t sidx[JS_CH];
-  uint32_t r_ox[JS_CH], r_oy[JS_CH];     // outer window (|dt| <= W): quantum range in tile positions
-  uint32_t r_zo[JS_CH], r_wo[JS_CH];     // inner window (|dt| <= min(W, 500 ms))
-  uint32_t r_x1[JS_CH], r_y1[JS_CH];     // quanta wholly inside the exact inner window
-  uint32_t r_z2[JS_CH], r_w2[JS_CH];     // +-250 ms part (tiers 2-3)
-  uint32_t P[JS_CH + 4];                 // pairs before span k
+  uint4 rg[JS_CH];     // x, y: inner window (|dt| <= min(W, 500 ms)) as tile positions; z, w: the quanta wholly inside it
+  uint4 rg2[JS_CH];    // x, y: the +-250 ms part (tiers 2-3); z, w: outer window (|dt| <= W)
+  uint2 spc[JS_CH];    // the span's (pod, service+node class)
   uint32_t n_note[JS_CH], n_tr[JS_CH], n_tr_in[JS_CH], n_match[JS_CH], n_low[JS_CH], n_edge[JS_CH], n_23[JS_CH], n_unl[JS_CH];
   uint16_t note[JS_LIST][JS_CH];
   uint32_t hkey[JS_HASH];
@@ -168,8 +166,8 @@ __host__ __device__ inline uint32_t slab_bytes_per_event(bool t32) { return t32 
 
 // The persistent CTA's work loop.  F: kept candidates held in registers; T32: every pair the kernel forms is closer
 // than 2^31 ns, so the low words of the times give exact differences.
-template <int F, bool T32>
-__global__ void __launch_bounds__(JS_THREADS, 2)
+template <int F, bool T32, int OCC>
+__global__ void __launch_bounds__(JS_THREADS, OCC)
 k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SlabFixed &sm = *reinterpret_cast<SlabFixed *>(smem_raw);
@@ -335,8 +333,10 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
       const int ns = (int)min((uint32_t)JS_CH, nS - c0);
       __syncthreads();   // the columns are complete / the previous sub-chunk is done with the span staging
       // ---- the sub-chunk's spans, their windows as positions of the tile, the trace-id hash
-      sm.hkey[tid] = 0;            // JS_THREADS == JS_HASH
-      sm.hhead[tid] = TM_END;
+      if (tid < JS_HASH) {
+        sm.hkey[tid] = 0;
+        sm.hhead[tid] = TM_END;
+      }
       if ((int)tid < ns) {
         const U8 u = ld_nc_v8(p.sp + S0 + c0 + tid);
         sm.span[tid][0] = u.a;
@@ -370,8 +370,9 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
             x1 = y1 = z2;   // no whole quantum inside the window (a quantum wider than it): everything is enumerated
           }
         }
-        sm.r_ox[tid] = ox; sm.r_oy[tid] = oy; sm.r_zo[tid] = zo; sm.r_wo[tid] = wo;
-        sm.r_x1[tid] = x1; sm.r_y1[tid] = y1; sm.r_z2[tid] = z2; sm.r_w2[tid] = w2;
+        sm.rg[tid] = make_uint4(zo, wo, x1, y1);
+        sm.rg2[tid] = make_uint4(z2, w2, ox, oy);
+        sm.spc[tid] = nq && u.a.z < jp.n_idents ? __ldg(jp.ident_pc + u.a.z) : make_uint2(0u, 0u);
       }
       __syncthreads();
       const bool uniform = sm.cls_min == sm.cls_max;
@@ -404,7 +405,7 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
         while ((key = sm.hkey[hs]) != 0u && key != tr) hs = (hs + 1) & (JS_HASH - 1);
         if (key != tr) continue;
         for (uint32_t k = sm.hhead[hs]; k != TM_END; k = sm.hnext[k]) {
-          if (o < sm.r_ox[k] || o >= sm.r_oy[k]) continue;             // outside the outer window's quanta
+          if (o < sm.rg2[k].z || o >= sm.rg2[k].w) continue;             // outside the outer window's quanta
           uint64_t adt;
           if (T32) {   // inside those quanta |dt| < W + quantum < 2^31
             const int32_t d = (int32_t)(q4[o].x - sm.span[k][0].x);
@@ -423,71 +424,68 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
         }
       }
       __syncthreads();
-      // ---- tiers 2-4: one warp per span, the lanes stride over the span's pairs.  Span data is warp-uniform, every
-      //      count is a ballot, and notes are appended at ballot ranks (no atomics, no per-lane loop state).
+      // ---- tiers 2-4: one warp per span, the lanes stride over the span's pairs.  Span data is warp-uniform (a few
+      //      broadcast loads of what the staging pass prepared), counts are kept per lane and summed once per span,
+      //      notes are appended at ballot ranks (no atomics).
       {
         const uint32_t Wi32 = (uint32_t)Wi;
         for (int k = (int)warp; k < ns; k += JS_THREADS / 32) {
-          const SpanRec s = span_from_halves(sm.span[k][0], sm.span[k][1]);
-          const uint32_t zo = sm.r_zo[k], wo = sm.r_wo[k];
+          const uint4 rg = sm.rg[k];
+          const uint32_t zo = rg.x, wo = rg.y, x1 = rg.z, y1 = rg.w;
           if (zo >= wo) continue;   // nothing inside the inner window (also: every span that can match nothing)
-          const uint2 spc = __ldg(jp.ident_pc + s.ident);
-          const bool pod_ok = spc.x != 0, pid_ok = s.pid != 0, conn_ok = s.conn != 0;
+          const uint4 sa = sm.span[k][0], sb = sm.span[k][1];
+          const uint2 spc = sm.spc[k];
+          const uint32_t s_lo = sa.x, s_pid = sa.w, s_conn = sb.x;
+          const int64_t s_ts = (int64_t)(((uint64_t)sa.y << 32) | sa.x);
+          const bool ok2 = spc.x != 0 && s_pid != 0, ok3 = spc.x != 0 && s_conn != 0;   // dns.go:61-68: non-empty pod, pid / conn
           const uint32_t s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
-          const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
-          const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;
+          const uint32_t no_trace = sb.y != 0 ? sb.y : 0xffffffffu;
           const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)jp.fanout;   // the kept list is already full of trace-id matches
-          const uint32_t x1 = sm.r_x1[k], y1 = sm.r_y1[k];
-          // segments that are enumerated: everything but the quanta wholly inside the window that lie outside +-250 ms
-          uint32_t a0 = zo, lenA = wo - zo, b0 = 0, lenB = 0, c0s = 0, lenC = 0;
+          // enumerated: everything but the quanta wholly inside the window that lie outside +-250 ms.  Pair j of the
+          // span sits at zo + j, shifted by the gaps it has passed.
+          uint32_t lenA = wo - zo, lenAB = lenA, total = lenA, gap1 = 0, gap2 = 0;
           if (counted) {
-            const uint32_t z2 = sm.r_z2[k], w2 = sm.r_w2[k];
-            lenA = min(x1, z2) - zo;
-            b0 = z2; lenB = w2 - z2;
-            c0s = max(y1, w2); lenC = wo - c0s;
+            const uint32_t z2 = sm.rg2[k].x, w2 = sm.rg2[k].y;
+            const uint32_t a1 = min(x1, z2), c0s = max(y1, w2);
+            lenA = a1 - zo; lenAB = lenA + (w2 - z2); total = lenAB + (wo - c0s);
+            gap1 = z2 - a1; gap2 = c0s - w2;
           }
-          const uint32_t lenAB = lenA + lenB, total = lenAB + lenC;
-          uint32_t n_note = sm.n_note[k];          // the probe's trace-id notes come first
-          uint32_t n_match = 0, n_low = 0, n_edge = 0, n_23 = 0, n_unl = 0;   // warp-uniform
+          uint32_t n_note = sm.n_note[k];          // the probe's trace-id notes come first (warp-uniform)
+          uint32_t c_match = 0, c_low = 0, c_edge = 0, n_unl = 0;   // per lane, except n_unl
           for (uint32_t jb = 0; jb < total; jb += 32) {
-            const uint32_t j = jb + lane;
-            const bool valid = j < total;
-            const uint32_t o = j < lenA ? a0 + j : (j < lenAB ? b0 + (j - lenA) : c0s + (j - lenAB));
-            uint4 e = make_uint4(0, 0, 0, 0);
-            uint32_t e_tr = 0;
-            if (valid) { e = q4[o]; e_tr = trs[o] >> 4; }
+            const uint32_t j = min(jb + lane, total - 1);
+            const bool valid = jb + lane < total;
+            const uint32_t o = zo + j + (j >= lenA ? gap1 : 0u) + (j >= lenAB ? gap2 : 0u);
+            const uint4 e = q4[o];
             bool in, in100, in250;
             if (T32) {
               const int32_t d = (int32_t)(e.x - s_lo);
               const uint32_t ad = (uint32_t)(d < 0 ? -d : d);
               in = ad <= Wi32; in100 = ad <= (uint32_t)(100 * kMs); in250 = ad <= (uint32_t)(250 * kMs);
             } else {
-              const uint64_t ad = valid ? lsg_absdiff(s.ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | e.x)) : ~0ull;
+              const uint64_t ad = lsg_absdiff(s_ts, (int64_t)(((uint64_t)ts_hi[o] << 32) | e.x));
               in = ad <= Wi; in100 = ad <= (uint64_t)(100 * kMs); in250 = ad <= (uint64_t)(250 * kMs);
             }
             in &= valid;
-            const bool same_pod = pod_ok & (e.y == spc.x);
-            const bool t2 = same_pod & pid_ok & (e.z == s.pid) & in100;        // dns.go:61-64
-            const bool t3 = same_pod & conn_ok & (e.w == s.conn) & in250;      // dns.go:65-68
+            const bool same_pod = e.y == spc.x;
+            const bool t2 = ok2 & same_pod & (e.z == s_pid) & in100;        // dns.go:61-64
+            const bool t3 = ok3 & same_pod & (e.w == s_conn) & in250;      // dns.go:65-68
             int tier;
             bool m;
             if (counted) {
               tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
-              m = in & (e_tr != no_trace) & (t2 | t3);
-              n_23 += __popc(__ballot_sync(0xffffffffu, m));
-              n_edge += __popc(__ballot_sync(0xffffffffu, in & ((o < x1) | (o >= y1))));
+              m = in & (t2 | t3);
+              c_edge += in & ((o < x1) | (o >= y1));
             } else {
-              const bool same_sn = valid && cls[o] == s_cls;
+              const bool same_sn = cls[o] == s_cls;
               tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
-              m = in & (e_tr != no_trace) & (tier != 0);
+              m = in & (tier != 0);
             }
-            const unsigned mm = __ballot_sync(0xffffffffu, m);
-            if (mm == 0) continue;
-            n_match += __popc(mm);
+            if (m) m = (trs[o] >> 4) != no_trace;   // a trace-id match belongs to tier 1 (the hash pass)
+            c_match += m;
             const bool low = m & (tier > cut);                                 // correlator.go:83-86
-            const unsigned lm = __ballot_sync(0xffffffffu, low);
-            n_low += __popc(lm);
-            const unsigned cm = mm & ~lm;                                      // candidates
+            c_low += low;
+            const unsigned cm = __ballot_sync(0xffffffffu, m & !low);          // candidates
             if (cm) {
               if (full) {
                 n_unl += __popc(cm);
@@ -500,8 +498,12 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
               }
             }
           }
+          c_match = __reduce_add_sync(0xffffffffu, c_match);
+          c_low = __reduce_add_sync(0xffffffffu, c_low);
+          c_edge = __reduce_add_sync(0xffffffffu, c_edge);
           if (lane == 0) {
-            sm.n_note[k] = n_note; sm.n_match[k] = n_match; sm.n_low[k] = n_low; sm.n_edge[k] = n_edge; sm.n_23[k] = n_23;
+            sm.n_note[k] = n_note; sm.n_match[k] = c_match; sm.n_low[k] = c_low; sm.n_edge[k] = c_edge;
+            sm.n_23[k] = counted ? c_match : 0u;   // in the counted form every enumerated match is a tier 2-3 match
             sm.n_unl[k] = n_unl;
           }
         }
@@ -608,9 +610,9 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
               if (counted) {
                 // what is left inside the exact inner window after the trace-id and pod matches is the service+node tier
                 // (below the threshold here: counted as matched and low-confidence, correlator.go:83-86)
-                const uint2 spc = __ldg(jp.ident_pc + s.ident);
+                const uint2 spc = sm.spc[k];
                 if (spc.y != 0 && spc.y == sm.cls_min) {
-                  const uint32_t n_in = (sm.r_y1[k] - sm.r_x1[k]) + sm.n_edge[k];
+                  const uint32_t n_in = (sm.rg[k].w - sm.rg[k].z) + sm.n_edge[k];
                   const uint32_t n4 = n_in - sm.n_23[k] - sm.n_tr_in[k];
                   n_match += n4;
                   n_low += n4;
