@@ -496,6 +496,8 @@ def measure_e2e(env, wl, args):
     torch, dist, ctx, stream, A = env["torch"], env["dist"], env["ctx"], env["stream"], env["A"]
     world = env["world"]
     local = env["local_counters"]
+    import llm_slo_ebpf_toolkit_b200 as pkg_mod
+    pkg_lib = pkg_mod.load_library()
 
     def barrier():
         stream.synchronize()
@@ -524,7 +526,22 @@ def measure_e2e(env, wl, args):
                     "inc_signals": pinned(wl.n_incidents * A.NSIG * 8), "posterior": pinned(wl.n_incidents * A.NDOM * 8),
                     "top1": pinned(wl.n_incidents), "counters": pinned(C.sizeof(A.Counters))}
 
-            def make(dense):
+            # the events once more in their 24-byte upload form (what an interner would emit; packed outside the timed region
+            # like every other input of the step)
+            import numpy as np
+            ev_np = host["events"].numpy().view(A.EVENT_DTYPE)
+            e24 = pinned(wl.n_events * 24)
+            e24_base = int(wl.args.span_ts_lo) - 2_000_000_000 if wl.args.key_hint else int(wl.cfg.t0_ns) - 2_000_000_000
+            misfit = pkg_lib.lsg_pack_events24(ev_np.ctypes.data, wl.n_events, e24_base, e24.numpy().ctypes.data)
+            host["events24"] = e24
+
+            def make(dense, compact_in=False):
+                a = make32(dense)
+                if compact_in and misfit == 0:
+                    a.events, a.events24, a.events24_base = None, e24.data_ptr(), e24_base
+                return a
+
+            def make32(dense):
                 return A.PipelineArgs(host["spans"].data_ptr(), wl.n_spans, host["events"].data_ptr(), wl.n_events,
                                       host["idents"].data_ptr(), wl.n_idents, wl.n_incidents, host["inc_actual"].data_ptr(),
                                       host["inc_expected"].data_ptr(), host["inc_expected_n"].data_ptr(), 0, 0.0, f, 0.10,
@@ -533,12 +550,13 @@ def measure_e2e(env, wl, args):
                                       outs["inc_signals"].data_ptr(), outs["posterior"].data_ptr(), outs["top1"].data_ptr(),
                                       outs["counters"].data_ptr(), None if dense else outs["cand_value"].data_ptr(),
                                       None if dense else outs["cand_sig"].data_ptr())
-            forms = {"dense": make(True), "compact": make(False)}
+            forms = {"dense": make(True), "compact": make(False), "compact24": make(False, True)}
             for a_ in forms.values():   # the same statement about the batch as in the device-resident steps
                 a_.key_hint, a_.max_grp_hint = wl.args.key_hint, wl.args.max_grp_hint
                 a_.span_ts_lo, a_.span_ts_hi = wl.args.span_ts_lo, wl.args.span_ts_hi
             slots.append((host, outs, forms))
-        h2d = sum(slots[0][0][k].numel() for k in slots[0][0])
+        h2d = sum(slots[0][0][k].numel() for k in slots[0][0] if k != "events24")
+        h2d24 = h2d - slots[0][0]["events"].numel() + slots[0][0]["events24"].numel()
         common = ("cand_event", "cand_tier", "inc_signals", "posterior", "top1", "counters")
         d2h = {"dense": sum(slots[0][1][k].numel() for k in common + ("attr", "conf")),
                "compact": sum(slots[0][1][k].numel() for k in common + ("cand_value", "cand_sig"))}
@@ -595,20 +613,26 @@ def measure_e2e(env, wl, args):
 
         sync_ms = blocking("dense")
         dense_ms = pipelined("dense")
-        e2e_ms = pipelined("compact")
+        rec32_ms = pipelined("compact")
+        e2e_ms = pipelined("compact24")
         if world > 1:
             flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             ok = bool(flag.item())
     rate = lambda ms_: wl.n_events * world * e2e_steps / (ms_ / 1e3)
-    return {"value": rate(e2e_ms), "unit": UNIT, "h2d_bytes_per_step": h2d,
+    return {"value": rate(e2e_ms), "unit": UNIT, "h2d_bytes_per_step": h2d24 if misfit == 0 else h2d,
             "d2h_bytes_per_step": d2h["compact"], "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
             "incidents_per_s": wl.n_incidents * world * e2e_steps / (e2e_ms / 1e3),
-            "api": "lsg_pipeline_submit/lsg_pipeline_wait, 2 batches in flight, pinned host buffers; per-span attributes "
-                   "as (signal, value) of the kept candidates (cand_sig / cand_value), dense rows not requested",
+            "api": "lsg_pipeline_submit/lsg_pipeline_wait, 2 batches in flight, pinned host buffers; events in the 24-byte "
+                   "upload form (lsg_event24, widened by the first device pass), spans / identities / incidents as "
+                   "they are; per-span attributes as (signal, value) of the kept candidates (cand_sig / cand_value), "
+                   "dense rows not requested",
+            "events24_misfit": int(misfit),
+            "records32": {"value": rate(rec32_ms), "ms_per_step": rec32_ms / e2e_steps, "h2d_bytes_per_step": h2d,
+                          "note": "same calls with the events uploaded as 32-byte lsg_event records"},
             "dense_outputs": {"value": rate(dense_ms), "ms_per_step": dense_ms / e2e_steps,
-                              "d2h_bytes_per_step": d2h["dense"],
-                              "note": "same calls with the dense 12-column attribute rows and the confidence column downloaded"},
+                              "d2h_bytes_per_step": d2h["dense"], "h2d_bytes_per_step": h2d,
+                              "note": "32-byte events up; the dense 12-column attribute rows and the confidence column down"},
             "sync_ms_per_step": sync_ms / e2e_steps, "sync_value": rate(sync_ms),
             "matches_device_run": bool(ok)}
 

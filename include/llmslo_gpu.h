@@ -74,6 +74,27 @@ typedef struct {
   uint32_t trace_sig; /* (interned TraceID << 4) | signal index (0..11, or LSG_SIG_UNSUPPORTED)   */
 } lsg_event;
 
+/* The same record in 24 bytes, for the upload: end to end a batch costs its PCIe transfer, not its kernels, so the
+ * form that crosses the bus is narrower than the one the kernels read (the first device pass widens it).  No reference
+ * counterpart (SignalRef is a Go struct of strings); the interner emits one or the other.  Limits of the narrow fields:
+ *   time      LSG_E24_TS_BITS-bit offset in ns from a per-batch `base` (73 minutes); all ones = the zero Time.  The
+ *             caller chooses base <= first span - window and needs last span + window < base + 2^42 - 1 (checked: the
+ *             pipeline refuses the batch otherwise); an event outside that range can match nothing and is encoded as
+ *             the zero Time
+ *   ident     < 2^14 identity rows,  pid < 2^22 (Linux PID_MAX_LIMIT),  trace id < 2^26,  conn id < 2^20 (ids are
+ *             per batch, so these bound the distinct values of one batch)
+ * lsg_pack_events24 reports how many records do not fit; a batch with any such record must go up in the 32-byte form. */
+#define LSG_E24_TS_BITS 42
+#define LSG_E24_IDENT_BITS 14
+#define LSG_E24_PID_BITS 22
+#define LSG_E24_TRACE_BITS 26
+#define LSG_E24_CONN_BITS 20
+typedef struct {
+  double value;
+  uint64_t a; /* time offset [0,42) | ident [42,56) | signal [56,60) | pid bits 0..3 [60,64) */
+  uint64_t b; /* trace id [0,26) | conn [26,46) | pid bits 4..21 [46,64)                      */
+} lsg_event24;
+
 /* SpanRef (dns.go:19-27) / SpanRecord (processor.go:10-20) after interning: 32 bytes. */
 typedef struct {
   int64_t ts_ns;
@@ -160,7 +181,7 @@ int lsg_host_alloc(size_t bytes, int write_combined, void **out);
 void lsg_host_free(void *p);
 
 /* sizeof() of the ABI structs as compiled into the library, in header order (event, span, ident, debug, eval,
- * model, confusion_out, feature, counters, pipeline_args, synth_cfg); returns how many there are.  Lets a
+ * model, confusion_out, feature, counters, pipeline_args, synth_cfg, event24); returns how many there are.  Lets a
  * binding check its own struct mirrors at load time. */
 int lsg_abi_sizes(size_t *out, int n);
 
@@ -313,6 +334,13 @@ typedef struct {
    * hold the batch's results are void and counters.bad_idents is non-zero. */
   uint32_t key_hint, max_grp_hint;
   int64_t span_ts_lo, span_ts_hi;
+  /* optional: the events in their 24-byte upload form instead of `events` (which may then be NULL); n_events counts them.
+   * Host pointer for lsg_pipeline / lsg_pipeline_submit, device pointer for lsg_pipeline_dev. */
+  const lsg_event24 *events24; int64_t events24_base;
+  /* optional (device for lsg_pipeline_dev, host otherwise): count / sum / log2 sketch per (incident, signal) of the
+   * spans' enriched attributes, [n_incidents * 12], accumulated in the join's epilogue next to the maxima.  Only the
+   * maxima (inc_signals) have a reference counterpart (correlator.go:109-111); these are this library's own features. */
+  lsg_feature *features_out;
 } lsg_pipeline_args;
 /* asynchronous: returns after enqueueing on the context's stream (without key_hint it synchronises once inside, after
  * the first reduction, to read the key layout back) */
@@ -328,6 +356,13 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *args, lsg_counters *coun
  * touched between submit and wait and should be pinned. */
 int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *args, int slot);
 int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out);
+
+/* ---- the 24-byte upload form (lsg_event24 above): host-side packing / unpacking of 32-byte records and the device pass
+ *      that widens them.  lsg_pack_events24 returns the number of records whose ident / pid / conn / trace id does not
+ *      fit the narrow fields (0 = the batch may go up in this form), < 0 on a bad argument.  No reference counterpart. */
+long long lsg_pack_events24(const lsg_event *events, size_t n, int64_t base, lsg_event24 *out);
+int lsg_unpack_events24(const lsg_event24 *in, size_t n, int64_t base, lsg_event *out);
+int lsg_widen_events24_dev(lsg_ctx *ctx, const lsg_event24 *in, size_t n, int64_t base, lsg_event *out);
 
 /* ---- per-kernel timing with CUDA events on the context's stream (bench.py's roofline numbers) ---------
  *  lsg_profile_read synchronises the stream, adds the finished intervals to per-kernel totals and copies

@@ -34,7 +34,9 @@ SPAN_DTYPE = np.dtype([("ts_ns", "<i8"), ("ident", "<u4"), ("pid", "<u4"), ("con
                        ("incident", "<u4"), ("reserved", "<u4")])
 IDENT_DTYPE = np.dtype([("pod", "<u4"), ("node", "<u4"), ("service", "<u4"), ("grp", "<u4")])
 FEATURE_DTYPE = np.dtype([("count", "<u4"), ("sketch", "<u4", (SKETCH_BINS,)), ("_pad", "<u4"), ("sum", "<f8")])
-assert EVENT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 32 and IDENT_DTYPE.itemsize == 16
+EVENT24_DTYPE = np.dtype([("value", "<f8"), ("a", "<u8"), ("b", "<u8")])   # lsg_event24: the 24-byte upload form
+E24_TS_BITS, E24_IDENT_BITS, E24_PID_BITS, E24_TRACE_BITS, E24_CONN_BITS = 42, 14, 22, 26, 20
+assert EVENT_DTYPE.itemsize == 32 and SPAN_DTYPE.itemsize == 32 and IDENT_DTYPE.itemsize == 16 and EVENT24_DTYPE.itemsize == 24
 
 
 class Debug(C.Structure):
@@ -77,7 +79,8 @@ class PipelineArgs(C.Structure):
                 ("cand_event", C.c_void_p), ("cand_tier", C.c_void_p), ("attr_out", C.c_void_p),
                 ("conf_out", C.c_void_p), ("inc_signals", C.c_void_p), ("posterior", C.c_void_p),
                 ("top1", C.c_void_p), ("counters_dev", C.c_void_p), ("cand_value", C.c_void_p), ("cand_sig", C.c_void_p),
-                ("key_hint", C.c_uint32), ("max_grp_hint", C.c_uint32), ("span_ts_lo", C.c_int64), ("span_ts_hi", C.c_int64)]
+                ("key_hint", C.c_uint32), ("max_grp_hint", C.c_uint32), ("span_ts_lo", C.c_int64), ("span_ts_hi", C.c_int64),
+                ("events24", C.c_void_p), ("events24_base", C.c_int64), ("features_out", C.c_void_p)]
 
 
 class SynthCfg(C.Structure):

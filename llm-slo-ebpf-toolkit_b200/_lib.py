@@ -48,6 +48,10 @@ def load_library():
         lib.lsg_launch_count.argtypes = [vp]
         lib.lsg_launch_count.restype = C.c_uint64
         lib.lsg_set_join_path.argtypes = [vp, cint]
+        lib.lsg_pack_events24.argtypes = [vp, sz, i64, vp]
+        lib.lsg_pack_events24.restype = C.c_longlong
+        lib.lsg_unpack_events24.argtypes = [vp, sz, i64, vp]
+        lib.lsg_widen_events24_dev.argtypes = [vp, vp, sz, i64, vp]
         lib.lsg_workspace_bytes.argtypes = [vp]
         lib.lsg_workspace_bytes.restype = sz
         lib.lsg_default_model.argtypes = [P(A.Model)]

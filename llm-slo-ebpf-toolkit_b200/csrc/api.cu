@@ -10,6 +10,7 @@
 
 static_assert(sizeof(lsg_event) == 32 && sizeof(lsg_span) == 32 && sizeof(lsg_ident) == 16, "record layout");
 static_assert(sizeof(lsg_feature) == 80, "feature layout");
+static_assert(sizeof(lsg_event24) == 24, "upload record layout");
 
 int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...) {
   char buf[512];
@@ -115,8 +116,18 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
                        const double *attr_base, uint32_t *cand_event, uint8_t *cand_tier, double *attr_out, double *conf_out,
                        double *retrieval_out, uint32_t *n_cand_out, uint64_t **join_counters_dev, SortedEvents *sorted,
                        unsigned long long *inc_keys = nullptr, size_t n_incidents = 0, double *cand_value = nullptr,
-                       uint8_t *cand_sig = nullptr, const LsgKeyHint *hint = nullptr) {
+                       uint8_t *cand_sig = nullptr, const LsgKeyHint *hint = nullptr, lsg_feature *feat = nullptr,
+                       const int64_t *e24_base = nullptr) {
   LSG_TRY(lsg_sort_events_prepare(ctx, events, n_events, idents, n_idents, window_ns, false, sorted, spans, n_spans, hint));
+  if (e24_base) {
+    // events that came up in the 24-byte form: their time offsets only reach from `base` to base + 2^42 - 2, which must
+    // cover everything a span can match (the key's time axis: first span - window .. last span + window)
+    const KeySpec &k = sorted->key;
+    if (k.ts_min <= k.ts_hi && (*e24_base > k.ts_min || (uint64_t)k.ts_hi - (uint64_t)*e24_base >= (((uint64_t)1 << LSG_E24_TS_BITS) - 1)))
+      return lsg_fail(ctx, LSG_ERR_RANGE, "events24_base %lld does not cover the spans' time range widened by the window "
+                      "[%lld, %lld] with a %d-bit offset", (long long)*e24_base, (long long)k.ts_min, (long long)k.ts_hi,
+                      LSG_E24_TS_BITS);
+  }
   void *small_v;
   LSG_TRY(lsg_ws(ctx, WS_SMALL, 4096, &small_v));
   // Two ways from here.  Default: permutation sort + the join that gathers its own tiles (the faster one as measured,
@@ -154,6 +165,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
     ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
     ja.ident_pc = ident_pc;
     ja.cand_value = cand_value; ja.cand_sig = cand_sig;
+    ja.feat = feat;
     LSG_TRY(lsg_launch_join_slab(ctx, ja, bev, bsp));
     *join_counters_dev = ja.counters;
     return 0;
@@ -187,6 +199,7 @@ int process_batch_core(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, cons
   ja.inc_keys = inc_keys; ja.n_incidents = n_incidents;
   ja.ident_pc = ident_pc;
   ja.cand_value = cand_value; ja.cand_sig = cand_sig;
+  ja.feat = feat;
   LSG_TRY(lsg_launch_join(ctx, ja));
   *join_counters_dev = ja.counters;
   return 0;
@@ -232,7 +245,7 @@ const char *lsg_version(void) { return "llmslo_gpu 0.1 (sm_100a)"; }
 int lsg_abi_sizes(size_t *out, int n) {
   const size_t v[] = {sizeof(lsg_event), sizeof(lsg_span), sizeof(lsg_ident), sizeof(lsg_debug), sizeof(lsg_eval),
                       sizeof(lsg_model), sizeof(lsg_confusion_out), sizeof(lsg_feature), sizeof(lsg_counters),
-                      sizeof(lsg_pipeline_args), sizeof(lsg_synth_cfg)};
+                      sizeof(lsg_pipeline_args), sizeof(lsg_synth_cfg), sizeof(lsg_event24)};
   const int m = (int)(sizeof v / sizeof v[0]);
   for (int i = 0; i < n && i < m; ++i) out[i] = v[i];
   return m;
@@ -307,7 +320,7 @@ void lsg_destroy(lsg_ctx *ctx) {
 static const char *kProfNames[PK_COUNT] = {"event_stats", "event_keys", "radix_hist", "radix_scan", "radix_scatter",
                                            "gather_events", "span_sort", "join", "incident_features", "attribute",
                                            "confusion", "match_pairs", "span_ranges", "bucket_count", "bucket_scatter",
-                                           "bucket_spans", "tile_list"};
+                                           "bucket_spans", "tile_list", "widen_events24"};
 int lsg_profile_enable(lsg_ctx *ctx, int on) {
   if (!ctx) return LSG_ERR_INVALID;
   ctx->prof = on != 0;
@@ -633,7 +646,7 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   if (!ctx || !a) return LSG_ERR_INVALID;
   // attr_out, conf_out, cand_value and cand_sig are optional outputs
   // an empty array may be NULL (a Go caller's empty slice): ProcessBatch with no signals returns the spans unchanged
-  if ((a->n_spans && (!a->spans || !a->cand_event || !a->cand_tier)) || (a->n_events && !a->events) ||
+  if ((a->n_spans && (!a->spans || !a->cand_event || !a->cand_tier)) || (a->n_events && !a->events && !a->events24) ||
       ((a->n_spans || a->n_events) && !a->idents) || !a->counters_dev ||
       (a->n_incidents && (!a->inc_signals || !a->posterior || !a->top1 || !a->inc_actual || !a->inc_expected ||
                           !a->inc_expected_n)))
@@ -651,10 +664,19 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
   void *acc = nullptr;
   LSG_TRY(lsg_ws(ctx, WS_FEAT, a->n_incidents * LSG_NSIG * 8, &acc));
   LSG_CUDA(ctx, cudaMemsetAsync(acc, 0, a->n_incidents * LSG_NSIG * 8, ctx->stream));
-  LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, a->events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
+  const lsg_event *events = a->events;
+  if (a->events24 && a->n_events) {   // the 24-byte upload form: widened once, every kernel reads 32-byte records
+    void *wide = nullptr;
+    LSG_TRY(lsg_ws(ctx, WS_EV_WIDE, a->n_events * sizeof(lsg_event), &wide));
+    LSG_TRY(lsg_launch_widen_events24(ctx, a->events24, a->n_events, a->events24_base, (lsg_event *)wide));
+    events = (const lsg_event *)wide;
+  }
+  if (a->features_out && a->n_incidents)
+    LSG_CUDA(ctx, cudaMemsetAsync(a->features_out, 0, a->n_incidents * LSG_NSIG * sizeof(lsg_feature), ctx->stream));
+  LSG_TRY(process_batch_core(ctx, a->spans, a->n_spans, events, a->n_events, a->idents, a->n_idents, window_ns, threshold,
                              fanout, nullptr, a->cand_event, a->cand_tier, a->attr_out, a->conf_out, nullptr, nullptr, &jc_dev,
                              &sorted, (unsigned long long *)acc, a->n_incidents, a->cand_value, a->cand_sig,
-                             a->key_hint ? &hint : nullptr));
+                             a->key_hint ? &hint : nullptr, a->features_out, a->events24 ? &a->events24_base : nullptr));
   LSG_TRY(lsg_launch_incident_finish(ctx, (const unsigned long long *)acc, a->n_incidents, a->inc_signals));
   LSG_TRY(lsg_launch_attribute(ctx, a->inc_signals, nullptr, nullptr, a->n_incidents, a->posterior, a->top1, nullptr));
   LSG_TRY(lsg_launch_confusion(ctx, a->inc_actual, a->top1, a->inc_expected, a->inc_expected_n, a->posterior, a->coverage_thr,
@@ -669,14 +691,20 @@ int lsg_pipeline_dev(lsg_ctx *ctx, const lsg_pipeline_args *a) {
 // makes the copies asynchronous); inputs go up, the pipeline runs, results come back, then it synchronises.
 int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counters_out) {
   if (!ctx || !a) return LSG_ERR_INVALID;
-  if ((a->n_spans && !a->spans) || (a->n_events && !a->events) || ((a->n_spans || a->n_events) && !a->idents) ||
+  if ((a->n_spans && !a->spans) || (a->n_events && !a->events && !a->events24) || ((a->n_spans || a->n_events) && !a->idents) ||
       (a->n_incidents && (!a->inc_actual || !a->inc_expected || !a->inc_expected_n)))
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
   LSG_TRY(set_device(ctx));
   const int f = a->fanout <= 0 ? 3 : a->fanout;
   lsg_pipeline_args d = *a;
   LSG_TRY(h2d(ctx, WS_SPANS_IN, a->spans, a->n_spans, &d.spans));
-  LSG_TRY(h2d(ctx, WS_EVENTS_IN, a->events, a->n_events, &d.events));
+  if (a->events24) {
+    d.events = nullptr;
+    LSG_TRY(h2d(ctx, WS_EVENTS_IN, a->events24, a->n_events, &d.events24));
+  } else {
+    LSG_TRY(h2d(ctx, WS_EVENTS_IN, a->events, a->n_events, &d.events));
+  }
+  LSG_TRY(dalloc(ctx, WS_IN5, a->features_out != nullptr, a->n_incidents * LSG_NSIG, &d.features_out));
   LSG_TRY(h2d(ctx, WS_IDENTS, a->idents, a->n_idents, &d.idents));
   LSG_TRY(h2d(ctx, WS_IN0, a->inc_actual, a->n_incidents, &d.inc_actual));
   LSG_TRY(h2d(ctx, WS_IN1, a->inc_expected, a->n_incidents, &d.inc_expected));
@@ -701,6 +729,7 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
   LSG_TRY(d2h(ctx, a->inc_signals, (const double *)d.inc_signals, a->n_incidents * LSG_NSIG));
   LSG_TRY(d2h(ctx, a->posterior, (const double *)d.posterior, a->n_incidents * LSG_NDOM));
   LSG_TRY(d2h(ctx, a->top1, (const uint8_t *)d.top1, a->n_incidents));
+  LSG_TRY(d2h(ctx, a->features_out, (const lsg_feature *)d.features_out, a->n_incidents * LSG_NSIG));
   LSG_CUDA(ctx, cudaMemcpyAsync(ctx->pinned, d.counters_dev, sizeof(lsg_counters), cudaMemcpyDeviceToHost, ctx->stream));
   LSG_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   if (counters_out) memcpy(counters_out, ctx->pinned, sizeof(lsg_counters));
@@ -720,8 +749,9 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *a, lsg_counters *counter
 // must stay untouched between submit and wait, and should be pinned (otherwise the copies serialise).
 }  // extern "C"
 namespace {
-enum { PB_EVENTS = 0, PB_SPANS, PB_IDENTS, PB_ACT, PB_EXP, PB_EXPN, PB_CE, PB_CT, PB_ATTR, PB_CONF, PB_SIG, PB_POST, PB_TOP1, PB_CNT, PB_CV, PB_CS, PB_BUFS };
-static_assert(PB_BUFS == 16, "WS_PIPE reserves 16 buffers per slot");
+enum { PB_EVENTS = 0, PB_SPANS, PB_IDENTS, PB_ACT, PB_EXP, PB_EXPN, PB_CE, PB_CT, PB_ATTR, PB_CONF, PB_SIG, PB_POST, PB_TOP1, PB_CNT, PB_CV, PB_CS,
+       PB_FEAT, PB_BUFS };
+static_assert(PB_BUFS <= 20, "WS_PIPE reserves 20 buffers per slot");
 
 int pipe_init(lsg_ctx *ctx) {
   if (ctx->up) return 0;
@@ -747,7 +777,7 @@ extern "C" {
 
 int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   if (!ctx || !a || slot < 0 || slot > 1) return LSG_ERR_INVALID;
-  if ((a->n_spans && !a->spans) || (a->n_events && !a->events) || ((a->n_spans || a->n_events) && !a->idents) ||
+  if ((a->n_spans && !a->spans) || (a->n_events && !a->events && !a->events24) || ((a->n_spans || a->n_events) && !a->idents) ||
       (a->n_incidents && (!a->inc_actual || !a->inc_expected || !a->inc_expected_n)))
     return lsg_fail(ctx, LSG_ERR_INVALID, "null argument");
   if (ctx->slot_busy[slot]) return lsg_fail(ctx, LSG_ERR_INVALID, "slot %d is still in flight: call lsg_pipeline_wait first", slot);
@@ -757,7 +787,9 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   lsg_pipeline_args d = *a;
   lsg_span *d_sp; lsg_event *d_ev; lsg_ident *d_id; uint8_t *d_act, *d_expn; uint32_t *d_exp;
   LSG_TRY(pipe_buf(ctx, slot, PB_SPANS, a->n_spans, &d_sp));
-  LSG_TRY(pipe_buf(ctx, slot, PB_EVENTS, a->n_events, &d_ev));
+  LSG_TRY(pipe_buf(ctx, slot, PB_EVENTS, a->n_events, &d_ev));   // (24-byte records use the front of the same buffer)
+  d.features_out = nullptr;
+  if (a->features_out) LSG_TRY(pipe_buf(ctx, slot, PB_FEAT, a->n_incidents * LSG_NSIG, &d.features_out));
   LSG_TRY(pipe_buf(ctx, slot, PB_IDENTS, a->n_idents, &d_id));
   LSG_TRY(pipe_buf(ctx, slot, PB_ACT, a->n_incidents, &d_act));
   LSG_TRY(pipe_buf(ctx, slot, PB_EXP, a->n_incidents, &d_exp));
@@ -778,7 +810,8 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
     if (bytes) LSG_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->up));
     return 0;
   };
-  LSG_TRY(up(d_ev, a->events, a->n_events * sizeof(lsg_event)));
+  if (a->events24) LSG_TRY(up(d_ev, a->events24, a->n_events * sizeof(lsg_event24)));
+  else LSG_TRY(up(d_ev, a->events, a->n_events * sizeof(lsg_event)));
   LSG_TRY(up(d_sp, a->spans, a->n_spans * sizeof(lsg_span)));
   LSG_TRY(up(d_id, a->idents, a->n_idents * sizeof(lsg_ident)));
   LSG_TRY(up(d_act, a->inc_actual, a->n_incidents));
@@ -786,7 +819,8 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   LSG_TRY(up(d_expn, a->inc_expected_n, a->n_incidents));
   LSG_CUDA(ctx, cudaEventRecord(ctx->ev_up[slot], ctx->up));
   // kernels
-  d.spans = d_sp; d.events = d_ev; d.idents = d_id; d.inc_actual = d_act; d.inc_expected = d_exp; d.inc_expected_n = d_expn;
+  d.events24 = a->events24 ? (const lsg_event24 *)d_ev : nullptr;
+  d.spans = d_sp; d.events = a->events24 ? nullptr : d_ev; d.idents = d_id; d.inc_actual = d_act; d.inc_expected = d_exp; d.inc_expected_n = d_expn;
   LSG_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_up[slot], 0));
   LSG_TRY(lsg_pipeline_dev(ctx, &d));
   LSG_CUDA(ctx, cudaEventRecord(ctx->ev_done[slot], ctx->stream));
@@ -805,6 +839,7 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   LSG_TRY(down(a->inc_signals, d.inc_signals, a->n_incidents * LSG_NSIG * 8));
   LSG_TRY(down(a->posterior, d.posterior, a->n_incidents * LSG_NDOM * 8));
   LSG_TRY(down(a->top1, d.top1, a->n_incidents));
+  LSG_TRY(down(a->features_out, d.features_out, a->n_incidents * LSG_NSIG * sizeof(lsg_feature)));
   LSG_TRY(down(ctx->slot_counters_host[slot], d.counters_dev, sizeof(lsg_counters)));
   LSG_CUDA(ctx, cudaEventRecord(ctx->ev_down[slot], ctx->down));
   ctx->slot_busy[slot] = true;

@@ -57,8 +57,10 @@ enum {
   WS_BK_TMP_ORIG,
   WS_BK_SUPER,       // two-level partition: super-bucket cursors
   WS_TILES,          // slab join: tile list
+  WS_EV_WIDE,        // events widened from the 24-byte upload form
+  WS_IN5,            // host-API staging: feature output
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
-  WS_PIPE_END = WS_PIPE + 2 * 16 - 1,
+  WS_PIPE_END = WS_PIPE + 2 * 20 - 1,
   WS_COUNT
 };
 
@@ -103,7 +105,7 @@ struct KeySpec {
 // per-kernel timing (bench.py's roofline): CUDA events recorded on the context's stream around each launch
 enum {
   PK_STATS = 0, PK_KEYS, PK_HIST, PK_SCAN, PK_SCATTER, PK_GATHER, PK_SPAN_SORT, PK_JOIN, PK_FEATURES, PK_ATTRIBUTE,
-  PK_CONFUSION, PK_PAIRS, PK_RANGES, PK_BK_COUNT, PK_BK_SCATTER, PK_BK_SPANS, PK_TILES, PK_COUNT
+  PK_CONFUSION, PK_PAIRS, PK_RANGES, PK_BK_COUNT, PK_BK_SCATTER, PK_BK_SPANS, PK_TILES, PK_WIDEN, PK_COUNT
 };
 struct ProfSpan { int kind; cudaEvent_t a, b; };
 
@@ -349,6 +351,7 @@ struct JoinArgs {
   unsigned long long *inc_keys; size_t n_incidents;
   const uint2 *ident_pc;   // lsg_ident_classes() of `idents`, or NULL: lsg_launch_join computes it
   double *cand_value; uint8_t *cand_sig;   // optional: value and signal of every kept candidate, [n_spans * fanout]
+  lsg_feature *feat = nullptr;             // optional: count / sum / sketch per (incident, signal), zeroed by the caller
 };
 int lsg_launch_join(lsg_ctx *, const JoinArgs &);
 // the slab join: events and spans bucketed by lsg_bucket_*; the JoinArgs fields about the sorted events (ev, span_perm)
@@ -357,6 +360,7 @@ int lsg_launch_join_slab(lsg_ctx *, const JoinArgs &, const Bucketed &ev, const 
 // per identity row: x = pod id, y = class of its (service, node) pair (0 when either is empty; equal pairs get
 // equal classes), so that the join compares two words per (span, event) pair instead of loading identity rows
 int lsg_ident_classes(lsg_ctx *, const lsg_ident *idents, size_t n_idents, const uint2 **out);
+int lsg_launch_widen_events24(lsg_ctx *, const lsg_event24 *in, size_t n, int64_t base, lsg_event *out);
 int lsg_launch_incident_finish(lsg_ctx *, const unsigned long long *keys, size_t n_incidents, double *signals_out);
 int lsg_launch_incident_features(lsg_ctx *, const double *span_attr, const uint32_t *span_incident, const lsg_span *spans,
                                  size_t n_spans, size_t n_incidents, double *signals_out, lsg_feature *features_out);

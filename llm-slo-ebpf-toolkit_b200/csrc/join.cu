@@ -74,7 +74,22 @@ struct JoinParams {
   unsigned long long *counters;  // [0] matched [1] low_confidence [2] fanout_dropped [3] candidates [4] kept [5] bad ident
   unsigned long long *inc_keys;
   size_t n_incidents;
+  lsg_feature *feat;             // optional: count / sum / log2 sketch per (incident, signal) next to the maxima
 };
+
+// one span's enriched value of one signal into the incident's features (the same bins as k_incident_accumulate)
+__device__ __forceinline__ void feat_add(lsg_feature *feat, size_t slot, double v) {
+  atomicAdd(&feat[slot].count, 1u);
+  atomicAdd(&feat[slot].sum, v);
+  int bin = 0;
+  if (v > 0) {
+    int ex;
+    frexp(v, &ex);
+    bin = ex - 1 + 4;
+    bin = bin < 0 ? 0 : (bin > LSG_SKETCH_BINS - 1 ? LSG_SKETCH_BINS - 1 : bin);
+  }
+  atomicAdd(&feat[slot].sketch[bin], 1u);
+}
 
 // ---- per-span event range --------------------------------------------------------------------------
 template <typename KeyT>
@@ -400,8 +415,10 @@ __device__ __forceinline__ void process_span(const JoinParams &p, const Cols c, 
   }
   if (lane < LSG_NSIG) {
     if (p.attr_out) p.attr_out[si * LSG_NSIG + lane] = val;
-    if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(val))
+    if (p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents && !isnan(val)) {
       atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + lane], f64_key(val));   // A7 glue: max per incident and signal
+      if (p.feat) feat_add(p.feat, (size_t)s.incident * LSG_NSIG + lane, val);
+    }
   }
   // llm.ebpf.correlation_confidence = max confidence = the first kept candidate's (correlator.go:113-118)
   const double v3 = __shfl_sync(0xffffffffu, val, 3), v4 = __shfl_sync(0xffffffffu, val, 4);
@@ -830,8 +847,10 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
                 if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
             }
             if (p.attr_out) p.attr_out[si * LSG_NSIG + col] = v;
-            if (to_incident && !isnan(v))
+            if (to_incident && !isnan(v)) {
               atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
+              if (p.feat) feat_add(p.feat, (size_t)s.incident * LSG_NSIG + col, v);
+            }
             if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
             if (c == 3) v3 = v;
             if (c == 4) v4 = v;
@@ -1019,6 +1038,7 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   p.cand_value = a.cand_value; p.cand_sig = a.cand_sig;
   p.counters = (unsigned long long *)a.counters;
   p.inc_keys = a.inc_keys; p.n_incidents = a.n_incidents;
+  p.feat = a.feat;
   const size_t n_chunks = (a.n_spans + JT_CH - 1) / JT_CH;
   const size_t smem = sizeof(TileSmem);
   // spans that do not fit a tile are listed for k_join_big; the list lives behind the ranges
@@ -1091,6 +1111,7 @@ int lsg_launch_join_slab(lsg_ctx *ctx, const JoinArgs &a, const Bucketed &ev, co
   j.cand_value = a.cand_value; j.cand_sig = a.cand_sig;
   j.counters = (unsigned long long *)a.counters;
   j.inc_keys = a.inc_keys; j.n_incidents = a.n_incidents;
+  j.feat = a.feat;
   p.ev = (const lsg_event *)ev.rec; p.ev_orig = ev.orig; p.ev_ends = ev.ends;
   p.sp = (const lsg_span *)sp.rec; p.sp_orig = sp.orig; p.sp_ends = sp.ends;
   p.n_buckets = ev.n_buckets;

@@ -597,8 +597,10 @@ k_join_slab(const __grid_constant__ SlabParams p, uint32_t *__restrict__ big_lis
                   if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
               }
               if (jp.attr_out) jp.attr_out[si * LSG_NSIG + col] = v;
-              if (to_incident && !isnan(v))
+              if (to_incident && !isnan(v)) {
                 atomicMax(&jp.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
+                if (jp.feat) feat_add(jp.feat, (size_t)s.incident * LSG_NSIG + col, v);
+              }
               if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
               if (c == 3) v3 = v;
               if (c == 4) v4 = v;

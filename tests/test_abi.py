@@ -33,10 +33,10 @@ def test_header_symbols_exported(lib):
 def test_struct_sizes_match_mirrors(lib):
     out = (C.c_size_t * 16)()
     m = lib.lsg_abi_sizes(out, 16)
-    assert m == 11
+    assert m == 12
     want = [A.EVENT_DTYPE.itemsize, A.SPAN_DTYPE.itemsize, A.IDENT_DTYPE.itemsize, C.sizeof(A.Debug), C.sizeof(A.Eval),
             C.sizeof(A.Model), C.sizeof(A.ConfusionOut), A.FEATURE_DTYPE.itemsize, C.sizeof(A.Counters),
-            C.sizeof(A.PipelineArgs), C.sizeof(A.SynthCfg)]
+            C.sizeof(A.PipelineArgs), C.sizeof(A.SynthCfg), A.EVENT24_DTYPE.itemsize]
     assert list(out[:m]) == want
 
 
@@ -79,3 +79,31 @@ def test_synth_host_is_deterministic_and_valid(lib):
     assert other["events"].tobytes() != ev.tobytes()
     with pytest.raises(ValueError):
         synth.generate_host(synth.config(10, 10, 7, 8, 2))
+
+
+def test_event24_pack_round_trip_and_limits(lib):
+    """The 24-byte upload form (lsg_event24): packing is exact inside the narrow fields' limits, the zero Time and
+    times the offset cannot express come back as the zero Time, and records that do not fit are counted."""
+    cfg = synth.config(20000, 2000, 64, 8, 2, seed=3)
+    ev = synth.generate_host(cfg)["events"]
+    base = int(cfg.t0_ns) - 2_000_000_000
+    ev["ts_ns"][:50] = A.TS_ZERO
+    ev["ts_ns"][50:60] = base - 1                       # before the base
+    ev["ts_ns"][60:70] = base + (1 << 42)               # beyond the offset's reach
+    ev["pid"][100] = (1 << 22) - 1
+    ev["conn"][101] = (1 << 20) - 1
+    packed = np.zeros(len(ev), A.EVENT24_DTYPE)
+    assert lib.lsg_pack_events24(ev.ctypes.data, len(ev), base, packed.ctypes.data) == 0
+    back = np.zeros(len(ev), A.EVENT_DTYPE)
+    assert lib.lsg_unpack_events24(packed.ctypes.data, len(ev), base, back.ctypes.data) == 0
+    want = ev.copy()
+    want["ts_ns"][50:70] = A.TS_ZERO
+    assert back.tobytes() == want.tobytes()
+    bad = ev.copy()
+    bad["ident"][5] = 1 << 14
+    bad["pid"][6] = 1 << 22
+    bad["conn"][7] = 1 << 20
+    bad["trace_sig"][8] = (1 << 26) << 4
+    assert lib.lsg_pack_events24(bad.ctypes.data, len(bad), base, packed.ctypes.data) == 4
+    lib.lsg_unpack_events24(packed.ctypes.data, len(bad), base, back.ctypes.data)
+    assert (back["ts_ns"][5:9] == A.TS_ZERO).all() and np.array_equal(back["trace_sig"][5:9] & 15, bad["trace_sig"][5:9] & 15)
