@@ -24,7 +24,7 @@
  * does not carry pod/node/service directly but an `ident`: a row of the identity table holding the
  * interned (pod, node, service) triple seen on that record, plus `grp`, the join group.
  *
- *   JOIN-GROUP CONTRACT (checked by nobody but the interner): any span/event pair for which the
+ *   JOIN-GROUP CONTRACT (lsg_validate_groups checks it for a batch): any span/event pair for which the
  *   reference Match() (pkg/correlation/dns.go:50-76) can return Matched must have the same
  *   non-zero grp.  The interner gets this by union-find over identity rows: rows sharing a
  *   non-empty pod, rows sharing a non-empty (service, node), and rows that carry the same
@@ -305,6 +305,9 @@ typedef struct {
   uint64_t bad_idents; /* non-zero: some event's or span's ident was outside the identity table (or the caller's key_hint
                           did not hold) and the batch's results are void.  lsg_pipeline and lsg_pipeline_wait turn it into LSG_ERR_RANGE; a caller of
                           lsg_pipeline_dev checks it after reading the counters back (summed over ranks it stays non-zero) */
+  uint64_t unsupported_events; /* events of an unsupported signal type (debug.unsupported_type = this x spans): what a caller
+                          that shards a batch needs to rebuild the whole batch's Unmatched / UnsupportedType, which count
+                          every (span, signal) pair, also those across shards (correlator.go:73-82) */
 } lsg_counters;
 #define LSG_COUNTER_WORDS (sizeof(lsg_counters) / 8)
 
@@ -356,6 +359,41 @@ int lsg_pipeline(lsg_ctx *ctx, const lsg_pipeline_args *args, lsg_counters *coun
  * touched between submit and wait and should be pinned. */
 int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *args, int slot);
 int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out);
+
+/* ---- a check of the JOIN-GROUP CONTRACT (top of this file) on a caller's batch: the library only pairs records of one
+ *      group, so groups that are too fine lose matches silently.  Match() (dns.go:50-76) can accept a pair on the trace
+ *      id, on the pod, or on the (service, node) pair; the contract holds exactly when each of those appears under one
+ *      group.  out[0] = identity rows whose non-empty pod was first seen under another group, out[1] = rows whose
+ *      non-empty (service, node) pair was, out[2] = spans / supported, timed events whose non-zero trace id was,
+ *      out[3] = records whose ident is outside the identity table.  All zero = the contract holds; a non-zero count says
+ *      it does not (how many records are counted depends on the order they are met in).  No reference counterpart. */
+int lsg_validate_groups(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                        const lsg_ident *idents, size_t n_idents, uint64_t out[4]);
+int lsg_validate_groups_dev(lsg_ctx *ctx, const lsg_span *spans, size_t n_spans, const lsg_event *events, size_t n_events,
+                            const lsg_ident *idents, size_t n_idents, uint64_t out[4] /* HOST */);
+
+/* ---- several GPUs of one box (no reference counterpart: the reference is one goroutine).  One context per
+ *      device inside the calling process; the caller shards the batch so that no join group is split (shard by node /
+ *      pod identity: Match() never pairs records of different groups, so every shard is a complete batch of its own) and
+ *      passes one lsg_pipeline_args per rank with HOST buffers, exactly as for lsg_pipeline.  All ranks upload, compute
+ *      and download at the same time; the one exchange is ncclAllReduce(ncclUint64, ncclSum) of the counter block.
+ *      counters_out[r] (optional) = rank r's own counters, reduced_out = their sum (ratios such as accuracy are formed
+ *      from the summed integers, so they do not depend on the reduction order) with debug.unmatched and
+ *      debug.unsupported_type put on the whole batch's footing: the reference counts every (span, signal) pair of the
+ *      batch (processor.go:29-49), also the pairs of a span and a signal that landed on different shards, which match
+ *      nothing; so reduced_out equals what one context returns for the concatenated batch.  NCCL is looked up at run time
+ *      (libnccl.so.2, or the path in LSG_NCCL_LIB) by lsg_multi_create; without it the call fails and the single-GPU
+ *      entry points are unaffected.  Devices must be distinct.  Not thread-safe.  On failure of lsg_multi_create `*out`
+ *      is still set when a handle exists: read lsg_multi_last_error, then lsg_multi_destroy. */
+typedef struct lsg_multi lsg_multi;
+int lsg_multi_create(const int *devices, int n_devices, lsg_multi **out);
+void lsg_multi_destroy(lsg_multi *m);
+const char *lsg_multi_last_error(const lsg_multi *m);
+int lsg_multi_size(const lsg_multi *m);
+lsg_ctx *lsg_multi_ctx(lsg_multi *m, int rank); /* rank r's context, e.g. for lsg_set_model; owned by the handle */
+int lsg_multi_nccl_version(void);               /* NCCL_VERSION_CODE of the library found, 0 = none */
+int lsg_multi_pipeline(lsg_multi *m, const lsg_pipeline_args *args /* n_devices */, lsg_counters *counters_out /* n_devices or NULL */,
+                       lsg_counters *reduced_out);
 
 /* ---- the 24-byte upload form (lsg_event24 above): host-side packing / unpacking of 32-byte records and the device pass
  *      that widens them.  lsg_pack_events24 returns the number of records whose ident / pid / conn / trace id does not

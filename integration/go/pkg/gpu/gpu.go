@@ -282,6 +282,7 @@ type Counters struct {
 	Confusion                               Confusion
 	Events, Spans, Incidents, Candidates, Kept uint64
 	BadIdents                               uint64
+	UnsupportedEvents                       uint64
 }
 
 // KeyHint is the optional statement about a batch (lsg_pipeline_args.key_hint): every span that can match has its time in

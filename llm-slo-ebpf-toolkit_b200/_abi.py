@@ -65,7 +65,8 @@ class ConfusionOut(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [("debug", Debug), ("confusion", ConfusionOut), ("events", C.c_uint64), ("spans", C.c_uint64),
-                ("incidents", C.c_uint64), ("candidates", C.c_uint64), ("kept", C.c_uint64), ("bad_idents", C.c_uint64)]
+                ("incidents", C.c_uint64), ("candidates", C.c_uint64), ("kept", C.c_uint64), ("bad_idents", C.c_uint64),
+                ("unsupported_events", C.c_uint64)]
 
 
 COUNTER_WORDS = C.sizeof(Counters) // 8

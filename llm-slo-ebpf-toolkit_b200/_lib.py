@@ -48,6 +48,17 @@ def load_library():
         lib.lsg_launch_count.argtypes = [vp]
         lib.lsg_launch_count.restype = C.c_uint64
         lib.lsg_set_join_path.argtypes = [vp, cint]
+        for name in ("lsg_validate_groups", "lsg_validate_groups_dev"):
+            getattr(lib, name).argtypes = [vp, vp, sz, vp, sz, vp, sz, P(C.c_uint64)]
+        lib.lsg_multi_create.argtypes = [P(cint), cint, P(vp)]
+        lib.lsg_multi_destroy.argtypes = [vp]
+        lib.lsg_multi_destroy.restype = None
+        lib.lsg_multi_last_error.argtypes = [vp]
+        lib.lsg_multi_last_error.restype = C.c_char_p
+        lib.lsg_multi_size.argtypes = [vp]
+        lib.lsg_multi_ctx.argtypes = [vp, cint]
+        lib.lsg_multi_ctx.restype = vp
+        lib.lsg_multi_pipeline.argtypes = [vp, P(A.PipelineArgs), P(A.Counters), P(A.Counters)]
         lib.lsg_pack_events24.argtypes = [vp, sz, i64, vp]
         lib.lsg_pack_events24.restype = C.c_longlong
         lib.lsg_unpack_events24.argtypes = [vp, sz, i64, vp]
@@ -263,6 +274,14 @@ class Context:
         b, sh, ps = C.c_uint32(), C.c_uint32(), C.c_uint32()
         self._check(self._lib.lsg_last_sort_info(self._h, C.byref(b), C.byref(sh), C.byref(ps)))
         return {"key_bits": b.value, "time_shift": sh.value, "passes": ps.value}
+
+    def validate_groups(self, spans, events, idents):
+        """The join-group contract on a batch: (pod conflicts, (service, node) conflicts, trace-id conflicts, bad idents)."""
+        spans, events, idents = _as(spans, A.SPAN_DTYPE), _as(events, A.EVENT_DTYPE), _as(idents, A.IDENT_DTYPE)
+        out = (C.c_uint64 * 4)()
+        self._check(self._lib.lsg_validate_groups(self._h, _ptr(spans), len(spans), _ptr(events), len(events), _ptr(idents),
+                                                  len(idents), out))
+        return tuple(int(x) for x in out)
 
     def set_join_path(self, path):
         """0: permutation sort + gathering join (default), 1: bucket partition + slab join, -1: LSG_JOIN_PATH decides."""

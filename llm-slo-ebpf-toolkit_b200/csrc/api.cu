@@ -216,7 +216,7 @@ void fill_debug(lsg_debug *d, const uint64_t *jc, const SortedEvents &sorted, ui
 __global__ void k_finalize_counters(const unsigned long long *__restrict__ jc, unsigned long long n_events,
                                     const LsgBatchStats *__restrict__ stats, unsigned long long n_spans,
                                     unsigned long long n_incidents, unsigned long long *__restrict__ out) {
-  // layout = lsg_counters: debug[4] | confusion | events spans incidents candidates kept bad_idents
+  // layout = lsg_counters: debug[4] | confusion | events spans incidents candidates kept bad_idents unsupported_events
   const int tail = 4 + (int)(sizeof(lsg_confusion_out) / 8);
   const unsigned long long n_unsupported = stats->n_unsupported;
   out[tail + 5] = (stats->bad != 0 || jc[5] != 0) ? 1ull : 0ull;
@@ -229,6 +229,7 @@ __global__ void k_finalize_counters(const unsigned long long *__restrict__ jc, u
   out[tail + 2] = n_incidents;
   out[tail + 3] = jc[3];
   out[tail + 4] = jc[4];
+  out[tail + 6] = n_unsupported;
 }
 
 __global__ void k_widen_keys(const uint32_t *__restrict__ in, size_t n, unsigned long long *__restrict__ out) {
@@ -845,6 +846,11 @@ int lsg_pipeline_submit(lsg_ctx *ctx, const lsg_pipeline_args *a, int slot) {
   ctx->slot_busy[slot] = true;
   return 0;
 }
+
+}  // extern "C"
+// multi.cu: the device copy of a slot's counter block (what the multi-GPU entry point allreduces)
+void *lsg_internal_slot_counters_dev(lsg_ctx *ctx, int slot) { return ctx->ws[WS_PIPE + slot * PB_BUFS + PB_CNT]; }
+extern "C" {
 
 int lsg_pipeline_wait(lsg_ctx *ctx, int slot, lsg_counters *counters_out) {
   if (!ctx || slot < 0 || slot > 1) return LSG_ERR_INVALID;
