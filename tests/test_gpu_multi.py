@@ -93,7 +93,8 @@ def test_multi_pipeline_equals_one_context_on_the_whole_batch(ctx):
         assert red.debug.as_tuple() == cw.debug.as_tuple()
         assert (red.events, red.spans, red.incidents, red.candidates, red.kept, red.unsupported_events, red.bad_idents) == \
             (cw.events, cw.spans, cw.incidents, cw.candidates, cw.kept, cw.unsupported_events, 0)
-        assert red.kept > 10_000 * n and red.unsupported_events == sum(100 * (r + 1) for r in range(n))
+        assert red.kept > 10_000 * n
+        assert red.unsupported_events == sum(int(((w["events"]["trace_sig"] & 15) >= A.NSIG).sum()) for w in shards) > 100 * n
         # a bad shard is reported with its rank, and the handle stays usable
         bad = shards[0]["events"].copy()
         bad["ident"][7] = 10_000
