@@ -10,6 +10,7 @@ Inputs (data fixtures of the reference, copied as data — they carry the refere
     pkg/benchmark/testdata/mixed_fault_samples.jsonl    4 label-only incidents (rule path)
 Outputs:
     labeled_pairs.json, multi_fault_samples.json, mixed_fault_samples.json : the records, verbatim
+    scenario_assertions.json : fault_profile and assertions of test/incident-lab/scenarios/*.yaml
     derived.json : results of oracle/ref_str.py on those records, kept as a regression pin next to
                    the independently extracted values of SURVEY.md §4 (checked in tests/test_oracle_str.py)
 """
@@ -63,6 +64,18 @@ def main():
     }
     with open(os.path.join(HERE, "derived.json"), "w") as f:
         json.dump(derived, f, indent=1, sort_keys=True)
+        f.write("\n")
+    # the incident-lab scenarios' fault profiles and `assertions:` blocks (test/incident-lab/scenarios/*.yaml), as data
+    import glob
+    import yaml
+    scen = {}
+    for path in sorted(glob.glob(os.path.join(REF, "test/incident-lab/scenarios/*.yaml"))):
+        with open(path) as f:
+            doc = yaml.safe_load(f)
+        scen[doc["name"]] = {"fault_profile": doc.get("fault_profile", {}), "assertions": doc.get("assertions", []),
+                             "sample_count": (doc.get("harness") or {}).get("sample_count")}
+    with open(os.path.join(HERE, "scenario_assertions.json"), "w") as f:
+        json.dump(scen, f, indent=1, sort_keys=True)
         f.write("\n")
     print("pairs:", {k: derived["pairs"][k] for k in ("tp", "fp", "fn", "tn", "mean_confidence", "tier_accuracy")})
     print("multi:", {k: derived["multi_fault"][k] for k in ("accuracy", "partial", "coverage_0.10")})
