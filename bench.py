@@ -125,6 +125,9 @@ def workload_cfg(name, rank, world):
     if name == "c3s":   # C3's shape at 1/10 of its size
         return synth.config(100_000_000, 5_000_000, 4096, 16, 2, 10, 1, horizon_ns=360 * SECOND, rank=rank, world=world), \
             "C3/10: 100M events x 5M spans, 4096 pods, multi-fault incidents"
+    if name == "c2g1":   # C2's size with every pod in ONE join group: what a trace id that spans all pods does to the grouping
+        return synth.config(10_000_000, 1_000_000, 64, 64, 64, 10, 0, rank=rank, world=world), \
+            "C2 size, one join group: 10M events x 1M spans, 64 pods in a single group (every span's window exceeds a tile)"
     if name == "small":
         return synth.config(1_000_000, 100_000, 64, 8, 2, 10, 0, horizon_ns=360 * SECOND, rank=rank, world=world), \
             "C2/10: 1M events x 100k spans (smoke-sized)"
@@ -404,7 +407,9 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
         try:   # DRAM bytes per launch of that kernel from the committed ncu --set full capture of this workload
             with open(os.path.join(ROOT, "profiles", "r02_ncu_traffic_%s.json" % name)) as fh:
                 capj = json.load(fh)
-            sass = {"join": "k_join_slab", "bucket_scatter": "k_bucket_scatter", "bucket_count": "k_bucket_count"}.get(dom)
+            sass = ({"join": "k_join_slab", "bucket_scatter": "k_bucket_scatter", "bucket_count": "k_bucket_count"} if slab else
+                    {"join": "k_join_tiles", "radix_hist": "k_count_keys" if "event_keys" not in per_kernel else "k_radix_hist",
+                     "radix_scatter": "k_place_events" if "event_keys" not in per_kernel else "k_radix_scatter"}).get(dom)
             if sass in capj["kernels"]:
                 traffic = capj["kernels"][sass]["dram_bytes_per_launch"]
                 cap_src = "ncu --set full capture at commit %s (profiles/r02_ncu_traffic_%s.json)" % (capj.get("commit", "?"), name)
@@ -484,7 +489,8 @@ def attribution_leg(env, n_inc, steps=5):
                         "25%% absent; lsg_attribute_dev + lsg_confusion_dev (each call synchronises)" % n_inc,
             "incidents_per_s": n_inc * world * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
             "hbm_frac": alg * steps / (ms / 1e3) / 1e9 / peak, "algorithmic_bytes_per_incident": alg / n_inc,
-            "checks": {"posteriors_sum_to_one": psum_ok, "confusion_n": int(out.n) == n_inc}}
+            "checks": {"posteriors_sum_to_one": psum_ok, "confusion_n": int(out.n) == n_inc,
+                       "verified": bool(psum_ok and int(out.n) == n_inc)}}
 
 
 def measure_e2e(env, wl, args):

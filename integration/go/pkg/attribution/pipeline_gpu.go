@@ -56,11 +56,21 @@ func (b *BayesianAttributor) model() gpu.Model {
 	return m
 }
 
+// lastModel is the model the library's default context holds (guarded by the context's own mutex: run is only
+// entered through it).
+var (
+	lastModel    gpu.Model
+	lastModelSet bool
+)
+
 func (b *BayesianAttributor) run(signals []map[string]float64, ruleLabel []uint8) ([]float64, []uint8, []uint16) {
 	ctx := gpu.MustDefault()
-	m := b.model()
-	if err := ctx.SetModel(&m); err != nil {
-		panic(err)
+	// the flattened model goes to the library only when Priors / Likelihoods changed since the last call
+	if m := b.model(); !lastModelSet || m != lastModel {
+		if err := ctx.SetModel(&m); err != nil {
+			panic(err)
+		}
+		lastModel, lastModelSet = m, true
 	}
 	n := len(signals)
 	arr := make([]float64, n*gpu.NSig)
@@ -232,14 +242,41 @@ func encode(samples []FaultSample, predictions []schema.IncidentAttribution) enc
 	return e
 }
 
-func confusion(samples []FaultSample, predictions []schema.IncidentAttribution, threshold float64) (gpu.Confusion, encoded) {
+// One round trip serves BuildConfusionMatrix, Accuracy, PartialAccuracy and CoverageAccuracy when they are called on
+// the same slices one after the other, as cmd/attributor (main.go:258-308) and pkg/benchmark (harness.go:85-113) do:
+// the last result is kept, keyed by the identity of the two slices and the coverage threshold (the matrix, the
+// accuracy and the partial numerators do not depend on the threshold).
+type confusionKey struct {
+	s0        *FaultSample
+	p0        *schema.IncidentAttribution
+	ns, np    int
+	threshold float64
+}
+
+var (
+	lastConfKey confusionKey
+	lastConfOut gpu.Confusion
+	lastConfEnc encoded
+	lastConfOK  bool
+)
+
+func confusion(samples []FaultSample, predictions []schema.IncidentAttribution, threshold float64, needCoverage bool) (gpu.Confusion, encoded) {
+	key := confusionKey{&samples[0], &predictions[0], len(samples), len(predictions), threshold}
+	if lastConfOK && key.s0 == lastConfKey.s0 && key.p0 == lastConfKey.p0 && key.ns == lastConfKey.ns && key.np == lastConfKey.np &&
+		(!needCoverage || key.threshold == lastConfKey.threshold) {
+		return lastConfOut, lastConfEnc
+	}
 	e := encode(samples, predictions)
 	out, err := gpu.MustDefault().ConfusionCounts(e.actual, e.pred, e.exp, e.expN, e.post, threshold, 0)
 	if err != nil {
 		panic(err)
 	}
+	lastConfKey, lastConfOut, lastConfEnc, lastConfOK = key, out, e, true
 	return out, e
 }
+
+// InvalidateConfusionCache drops the kept result; call it after mutating samples or predictions in place.
+func InvalidateConfusionCache() { lastConfOK = false }
 
 // BuildConfusionMatrix returns matrix counts keyed by actual/predicted fault domain (GPU build of pipeline.go:65-82).
 func BuildConfusionMatrix(samples []FaultSample, predictions []schema.IncidentAttribution) map[MatrixKey]int {
@@ -247,7 +284,7 @@ func BuildConfusionMatrix(samples []FaultSample, predictions []schema.IncidentAt
 	if len(samples) == 0 || len(predictions) == 0 {
 		return matrix
 	}
-	out, e := confusion(samples, predictions, 0)
+	out, e := confusion(samples, predictions, 0, false)
 	for a := 0; a < gpu.MaxActual; a++ {
 		for p := 0; p < gpu.NDom; p++ {
 			if c := out.Matrix[a][p]; c != 0 {
@@ -263,7 +300,7 @@ func Accuracy(samples []FaultSample, predictions []schema.IncidentAttribution) f
 	if len(predictions) == 0 || len(samples) == 0 {
 		return 0
 	}
-	out, _ := confusion(samples, predictions, 0)
+	out, _ := confusion(samples, predictions, 0, false)
 	return float64(out.Correct) / float64(len(predictions))
 }
 
@@ -272,7 +309,7 @@ func PartialAccuracy(samples []FaultSample, predictions []schema.IncidentAttribu
 	if len(predictions) == 0 || len(samples) == 0 {
 		return 0
 	}
-	out, _ := confusion(samples, predictions, 0)
+	out, _ := confusion(samples, predictions, 0, false)
 	return float64(out.Partial) / float64(len(predictions))
 }
 
@@ -282,7 +319,7 @@ func CoverageAccuracy(samples []FaultSample, predictions []schema.IncidentAttrib
 	if len(predictions) == 0 || len(samples) == 0 {
 		return 0
 	}
-	out, e := confusion(samples, predictions, threshold)
+	out, e := confusion(samples, predictions, threshold, true)
 	total := 0.0
 	for f := 0; f <= gpu.NDom; f++ {
 		for ln := 1; ln <= gpu.NDom; ln++ {
