@@ -105,7 +105,7 @@ func MustDefault() *Ctx {
 }
 
 func New(device int) (*Ctx, error) {
-	var sizes [11]C.size_t
+	var sizes [12]C.size_t
 	C.lsg_abi_sizes(&sizes[0], C.int(len(sizes)))
 	if uintptr(sizes[0]) != unsafe.Sizeof(Event{}) || uintptr(sizes[1]) != unsafe.Sizeof(Span{}) ||
 		uintptr(sizes[2]) != unsafe.Sizeof(Ident{}) || uintptr(sizes[3]) != unsafe.Sizeof(Debug{}) ||
@@ -337,4 +337,137 @@ func (c *Ctx) Pipeline(spans []Span, events []Event, idents []Ident, incActual [
 	}
 	rc := C.lsg_pipeline(c.h, &a, (*C.lsg_counters)(unsafe.Pointer(&r.Counters)))
 	return r, c.err(rc)
+}
+
+// ---- round 2 additions to the C ABI -------------------------------------------------------------------------------
+
+// Event24 is lsg_event24: the 24-byte upload form of an Event (time offset from a per-batch base, narrow ids).
+type Event24 struct {
+	Value float64
+	A, B  uint64
+}
+
+// PackEvents24 packs 32-byte records for the upload (lsg_pack_events24).  misfit > 0: some record does not fit the narrow
+// fields and the batch has to go up as 32-byte records.  An interner can emit Event24 directly and skip this pass.
+func PackEvents24(events []Event, base int64) (out []Event24, misfit int64) {
+	out = make([]Event24, len(events))
+	misfit = int64(C.lsg_pack_events24((*C.lsg_event)(ptr(events)), C.size_t(len(events)), C.int64_t(base),
+		(*C.lsg_event24)(ptr(out))))
+	return out, misfit
+}
+
+// SetJoinPath selects the implementation of the sort + join stages (0 permutation sort + gathering join, 1 bucket
+// partition + slab join, -1 the LSG_JOIN_PATH environment variable decides).
+func (c *Ctx) SetJoinPath(path int) error {
+	defer c.enter()()
+	return c.err(C.lsg_set_join_path(c.h, C.int(path)))
+}
+
+// ValidateGroups checks the join-group contract on a batch (lsg_validate_groups): identity rows whose pod /
+// (service, node) pair, and records whose trace id, were first seen under another group; idents outside the table.
+// All zero = the contract holds.  The interner's own output always passes; use it on batches packed elsewhere.
+func (c *Ctx) ValidateGroups(spans []Span, events []Event, idents []Ident) (pod, class, trace, badIdent uint64, err error) {
+	defer c.enter()()
+	var out [4]C.uint64_t
+	rc := C.lsg_validate_groups(c.h, (*C.lsg_span)(ptr(spans)), C.size_t(len(spans)), (*C.lsg_event)(ptr(events)),
+		C.size_t(len(events)), (*C.lsg_ident)(ptr(idents)), C.size_t(len(idents)), &out[0])
+	return uint64(out[0]), uint64(out[1]), uint64(out[2]), uint64(out[3]), c.err(rc)
+}
+
+// Multi wraps lsg_multi: one context per GPU of the box, NCCL allreduce of the counter block inside the library.
+type Multi struct {
+	mu sync.Mutex
+	h  *C.lsg_multi
+	n  int
+}
+
+// NewMulti creates one context per listed device (distinct ordinals).
+func NewMulti(devices []int) (*Multi, error) {
+	dv := make([]C.int, len(devices))
+	for i, d := range devices {
+		dv[i] = C.int(d)
+	}
+	var h *C.lsg_multi
+	if rc := C.lsg_multi_create(&dv[0], C.int(len(dv)), &h); rc != 0 {
+		msg := "invalid device list"
+		if h != nil {
+			msg = C.GoString(C.lsg_multi_last_error(h))
+			C.lsg_multi_destroy(h)
+		}
+		return nil, fmt.Errorf("llmslo_gpu: %s (code %d)", msg, int(rc))
+	}
+	return &Multi{h: h, n: len(devices)}, nil
+}
+
+func (m *Multi) Close() {
+	m.mu.Lock()
+	defer m.mu.Unlock()
+	if m.h != nil {
+		C.lsg_multi_destroy(m.h)
+		m.h = nil
+	}
+}
+
+// Shard is one rank's part of a batch: no join group may be split between shards (shard by node / pod identity).
+type Shard struct {
+	Spans                     []Span
+	Events                    []Event
+	Idents                    []Ident
+	IncActual, IncExpectedN   []uint8
+	IncExpected               []uint32
+}
+
+// Pipeline runs the whole path on every shard at once and returns each rank's results and the batch's counters
+// (lsg_multi_pipeline: the sum of the ranks' counters with Unmatched / UnsupportedType on the whole batch's footing,
+// i.e. what ProcessBatch + BuildConfusionMatrix return for the concatenated batch).
+func (m *Multi) Pipeline(shards []Shard, windowNS int64, threshold float64, fanout int, coverageThr float64) ([]PipelineResult, Counters, error) {
+	m.mu.Lock()
+	runtime.LockOSThread()
+	defer func() { runtime.UnlockOSThread(); m.mu.Unlock() }()
+	if len(shards) != m.n {
+		return nil, Counters{}, fmt.Errorf("llmslo_gpu: %d shards for %d devices", len(shards), m.n)
+	}
+	if fanout <= 0 {
+		fanout = 3
+	}
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	keep := func(p unsafe.Pointer) unsafe.Pointer {
+		if p != nil {
+			pin.Pin(p)
+		}
+		return p
+	}
+	// the argument structs live in C memory, so only pinned Go memory is referenced from them
+	args := (*[1 << 10]C.lsg_pipeline_args)(C.calloc(C.size_t(m.n), C.size_t(unsafe.Sizeof(C.lsg_pipeline_args{}))))
+	defer C.free(unsafe.Pointer(args))
+	res := make([]PipelineResult, m.n)
+	for r, sh := range shards {
+		ns, ni := len(sh.Spans), len(sh.IncActual)
+		res[r] = PipelineResult{Fanout: fanout, CandEvent: make([]uint32, ns*fanout), CandTier: make([]uint8, ns*fanout),
+			CandSig: make([]uint8, ns*fanout), CandValue: make([]float64, ns*fanout), IncSignals: make([]float64, ni*NSig),
+			Posterior: make([]float64, ni*NDom), Top1: make([]uint8, ni)}
+		a := &args[r]
+		a.spans, a.n_spans = (*C.lsg_span)(keep(ptr(sh.Spans))), C.size_t(ns)
+		a.events, a.n_events = (*C.lsg_event)(keep(ptr(sh.Events))), C.size_t(len(sh.Events))
+		a.idents, a.n_idents = (*C.lsg_ident)(keep(ptr(sh.Idents))), C.size_t(len(sh.Idents))
+		a.n_incidents = C.size_t(ni)
+		a.inc_actual, a.inc_expected = (*C.uint8_t)(keep(ptr(sh.IncActual))), (*C.uint32_t)(keep(ptr(sh.IncExpected)))
+		a.inc_expected_n = (*C.uint8_t)(keep(ptr(sh.IncExpectedN)))
+		a.window_ns, a.threshold, a.fanout, a.coverage_thr = C.int64_t(windowNS), C.double(threshold), C.int(fanout), C.double(coverageThr)
+		a.cand_event, a.cand_tier = (*C.uint32_t)(keep(ptr(res[r].CandEvent))), (*C.uint8_t)(keep(ptr(res[r].CandTier)))
+		a.cand_sig, a.cand_value = (*C.uint8_t)(keep(ptr(res[r].CandSig))), (*C.double)(keep(ptr(res[r].CandValue)))
+		a.inc_signals, a.posterior = (*C.double)(keep(ptr(res[r].IncSignals))), (*C.double)(keep(ptr(res[r].Posterior)))
+		a.top1 = (*C.uint8_t)(keep(ptr(res[r].Top1)))
+	}
+	own := make([]Counters, m.n)
+	var red Counters
+	rc := C.lsg_multi_pipeline(m.h, &args[0], (*C.lsg_counters)(unsafe.Pointer(&own[0])), (*C.lsg_counters)(unsafe.Pointer(&red)))
+	if rc != 0 {
+		return nil, red, fmt.Errorf("llmslo_gpu: %s (code %d)", C.GoString(C.lsg_multi_last_error(m.h)), int(rc))
+	}
+	for r := range res {
+		res[r].Counters = own[r]
+	}
+	return res, red, nil
 }
