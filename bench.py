@@ -210,6 +210,37 @@ def run_reference(args, out):
     return 0
 
 
+def numa_bind(cuda_index):
+    """Run this rank on the CPUs of its GPU's NUMA node, before any pinned buffer is allocated (first touch places the
+    pages on that node): with eight ranks uploading at once, buffers on the far socket halve a GPU's PCIe rate.
+    Returns what was done, for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = [x for x in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if x.strip()]
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(vis[cuda_index]) if cuda_index < len(vis) and vis[cuda_index].isdigit() else cuda_index)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dev = "/sys/bus/pci/devices/" + bus.lower()[-12:]
+        with open(dev + "/numa_node") as f:
+            node = int(f.read().strip())
+        with open(dev + "/local_cpulist") as f:
+            cpulist = f.read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        use = (cpus & allowed) or allowed
+        os.sched_setaffinity(0, use)
+        return {"gpu_numa_node": node, "cpus": len(use), "pci": bus, "_all_cpus": sorted(allowed)}
+    except Exception as e:   # no NVML / no sysfs: run where the launcher put us
+        return {"unbound": "%s: %s" % (type(e).__name__, e)}
+
+
 def _claim_stdout():
     """Libraries (NCCL prints its version) write to fd 1; the contract is ONE JSON line there.  Keep a private handle
     on the real stdout for that line and point fd 1 at stderr for everything else."""
@@ -673,6 +704,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: this path has no CPU fallback")
+    numa = numa_bind(local) if os.environ.get("LSG_NO_NUMA_BIND") is None else {"unbound": "LSG_NO_NUMA_BIND"}
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -694,8 +726,11 @@ def main():
 
     # ---- CPU baseline on the host cores (rank 0, N = 1) ---------------------------------------------
     cpu_baseline = None
+    all_cpus = numa.pop("_all_cpus", None)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cpu as O
+        if all_cpus:
+            os.sched_setaffinity(0, all_cpus)   # the CPU baseline uses every host core, not only the GPU's node
         threads = max(1, O.hw_threads())
         ne, ns = 2_000_000, 200_000
         w = O.generate_host(sample_cfg(ne, ns))
@@ -743,7 +778,8 @@ def main():
                        "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((r["events_per_gpu"] + r["spans_per_gpu"]) * 32 / 1e6),
                        "sort": r["sort"],
                        "key_hint": "spans' time range and group count stated by the caller (checked on the device; --no-key-hint reads the key layout back instead)" if not args.no_key_hint else "none",
-                       "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS)},
+                       "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS),
+                       "numa": numa},
             "e2e": e2e,
             "gpu_launches": r["gpu_launches"],
             "roofline": r["roofline"],
