@@ -1124,9 +1124,9 @@ int lsg_launch_join_slab(lsg_ctx *ctx, const JoinArgs &a, const Bucketed &ev, co
   void *tv = nullptr, *bv = nullptr;
   LSG_TRY(lsg_ws(ctx, WS_TILES, 64 + ((size_t)n_cuts + n_dead_chunks) * sizeof(uint2), &tv));
   LSG_TRY(lsg_ws(ctx, WS_RANGES, a.n_spans * sizeof(uint32_t) + 64, &bv));
-  uint32_t *hdr = (uint32_t *)tv;   // [0] tiles listed, [1] tiles taken
+  uint32_t *hdr = (uint32_t *)tv;   // [0] tiles listed
   uint2 *tiles = (uint2 *)((char *)tv + 64);
-  p.tiles = tiles; p.n_tiles = hdr; p.next_tile = hdr + 1;
+  p.tiles = tiles; p.n_tiles = hdr;
   uint32_t *big_list = (uint32_t *)bv;
   unsigned int *big_count = (unsigned int *)(a.counters + 6);
   {

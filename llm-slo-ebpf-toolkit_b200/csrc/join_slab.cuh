@@ -5,20 +5,23 @@
 // A bucket is one join group x 64 time quanta, a little longer than the window, so everything a span of bucket b can
 // match lies in buckets b-1 .. b+1 of its group.  A tile is a run of consecutive buckets of one group (its "core")
 // plus one halo bucket on each side:
-//   stage   the tile's events are one contiguous piece of the bucketed array: sequential 256-bit loads (an L2
-//           prefetch of the next tile's piece is issued with cp.async.bulk.prefetch while this one is worked on).
-//           Inside a bucket the events are in no particular order, so staging is a counting sort by time quantum
-//           in shared memory: pass A takes every event's quantum and its rank (shared-memory atomic), a scan
-//           turns the counts into quantum starts, pass B writes the columns at start + rank.
+//   stage   the tile's events are one contiguous piece of the bucketed array: sequential 256-bit loads.  Inside a
+//           bucket the events are in no particular order, so staging is a counting sort by time quantum in shared
+//           memory: pass A takes every event's quantum and its rank (shared-memory atomic), a scan turns the counts
+//           into quantum starts, pass B reads the records again (L2) and writes the columns at start + rank.
 //   ranges  a span's inner window, its +-250 ms part and the quanta wholly inside the window are reads of that
 //           quantum table: no global range table, no binary search.
 //   tier 1  (dns.go:58-60) hash join as in k_join_tiles: the sub-chunk's span trace ids in a 256-slot hash, every
 //           staged event probes it once.
-//   tiers 2-4 (dns.go:61-73) the (span, event) pairs of a sub-chunk of 128 spans are laid end to end and cut into
-//           equal slices, one per thread (merge-path style): every lane does the same number of pairs whatever the
-//           spans' own counts are.  One 128-bit shared load brings (time, pod, pid, conn) of an event.
+//   tiers 2-4 (dns.go:61-73) one warp per span of a sub-chunk of 128 spans, the lanes stride over the span's pairs:
+//           31 of 32 lanes busy whatever the spans' own counts are.  One 128-bit shared load brings (time, pod, pid,
+//           conn) of an event; counts are kept per lane and summed once per span, notes are appended at ballot ranks.
+//           (Equal per-thread slices of the sub-chunk's pairs laid end to end — merge-path style — were measured
+//           first: the nested per-thread loops diverge and ran at 12 of 32 lanes.)
 //   order / outputs   as k_join_tiles: notes of two bytes, ordered afterwards in registers under the reference's
 //           (confidence desc, |dt| asc, input order), two lanes per span.
+// Tiles are cut from the list by every warp on its own (same reads, same result: nothing to exchange), strided over the
+// persistent CTAs.
 // Spans that do not fit (a bucket with its halos larger than a tile, more notes than the list holds, fanout > 8) go
 // to k_join_big_slab: one warp per span over its three buckets straight from global memory.
 
@@ -43,7 +46,6 @@ struct SlabParams {
   KeySpec ks;
   const uint2 *tiles;        // (first bucket, end bucket); first == n_buckets: chunk `end` of the dead spans
   const uint32_t *n_tiles;
-  unsigned int *next_tile;   // work counter
   uint32_t cap;              // events per tile
 };
 
@@ -157,7 +159,6 @@ struct SlabFixed {
   uint32_t qs[JS_QCAP + 8];              // quantum starts (counts while they are taken)
   uint32_t scan_w[JS_THREADS / 32];
   uint32_t cls_min, cls_max;
-  uint32_t u_tile, u_b1, u_bc, u_be, u_lo, u_hi, u_E0, u_nE, u_S0, u_nS, u_kind;   // the unit being worked on
   unsigned long long cnt[5];
 };
 constexpr uint32_t JS_UNIT_DONE = 0, JS_UNIT_TILE = 1, JS_UNIT_BIG = 2, JS_UNIT_DEAD = 3;
