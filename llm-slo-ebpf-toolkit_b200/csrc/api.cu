@@ -289,6 +289,7 @@ int lsg_create(int device, void *stream, lsg_ctx **out) {
   lsg_default_model(&m);
   build_dev_model(&m, &ctx->model);
   ctx->model_set = true;
+  ctx->model_table_valid = false;
   *out = ctx;
   return 0;
 }
@@ -415,6 +416,7 @@ int lsg_set_model(lsg_ctx *ctx, const lsg_model *model) {
   if (!ctx || !model) return LSG_ERR_INVALID;
   build_dev_model(model, &ctx->model);
   ctx->model_set = true;
+  ctx->model_table_valid = false;
   return 0;
 }
 

@@ -2,6 +2,7 @@
 // K-confusion (pkg/attribution/pipeline.go:65-185).
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -74,14 +75,62 @@ __global__ void __launch_bounds__(256) k_incident_finish(const unsigned long lon
 }
 
 // ---- K-bayes ---------------------------------------------------------------------------------------
-// One thread per incident.  elevated[s] = value >= thresh[s] (bayesian.go:220-225);
+// elevated[s] = value >= thresh[s] (bayesian.go:220-225);
 // logP[d] = log prior + sum_s log clamp(elevated ? p : 1-p) (bayesian.go:230-242) with the logs taken
 // on the host, summed in the fixed order prior, signals 0..11, extra; log-sum-exp in AllDomains order
 // (bayesian.go:245-256); top-1 = first maximum of the posteriors (sort.SliceStable, bayesian.go:279-281).
+//
+// Given the model, the posteriors are a function of the 12-bit elevated mask alone: 4096 possible rows.  Small batches
+// compute them per incident (k_attribute); large ones (attribution alone over tens of millions of incidents, where the
+// fp64 exp / log of the direct form is what bounds the kernel, not HBM) read them from a table that the SAME device
+// function filled for every mask (k_attribute_table), so both forms return identical bits.
+__device__ __forceinline__ int posterior_of_mask(const DevModel &m, const unsigned elev, double po[LSG_NDOM]) {
+  double lp[LSG_NDOM];
+  double mx = -INFINITY;
+#pragma unroll
+  for (int d = 0; d < LSG_NDOM; ++d) {
+    double a = m.log_prior[d];
+#pragma unroll
+    for (int s = 0; s < LSG_NSIG; ++s) {
+      if (m.sig_mask >> s & 1) a = __dadd_rn(a, (elev >> s & 1) ? m.log_elev[s][d] : m.log_not[s][d]);
+    }
+    a = __dadd_rn(a, m.log_extra[d]);
+    lp[d] = a;
+    mx = a > mx ? a : mx;
+  }
+  double se = 0.0;
+#pragma unroll
+  for (int d = 0; d < LSG_NDOM; ++d) se = __dadd_rn(se, exp(lp[d] - mx));
+  const double logz = mx + log(se);
+  int best = 0;
+  double bestp = -1.0;
+#pragma unroll
+  for (int d = 0; d < LSG_NDOM; ++d) {
+    const double pd = exp(lp[d] - logz);
+    po[d] = pd;
+    if (pd > bestp) { bestp = pd; best = d; }
+  }
+  return best;
+}
+
+constexpr unsigned AT_MASKS = 1u << LSG_NSIG;
+
+__global__ void __launch_bounds__(128)
+k_attribute_table(const __grid_constant__ DevModel m, double *__restrict__ table, uint8_t *__restrict__ best) {
+  const unsigned e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= AT_MASKS) return;
+  double po[LSG_NDOM];
+  best[e] = (uint8_t)posterior_of_mask(m, e, po);
+#pragma unroll
+  for (int d = 0; d < LSG_NDOM; ++d) table[(size_t)e * LSG_NDOM + d] = po[d];
+}
+
+// One thread per incident.  TABLE: the posteriors come from k_attribute_table's rows (L2-resident, 256 KB).
+template <bool TABLE>
 __global__ void __launch_bounds__(128)
 k_attribute(const __grid_constant__ DevModel m, const double *__restrict__ signals, const uint8_t *__restrict__ has_signals,
             const uint8_t *__restrict__ rule_label, size_t n, double *__restrict__ posterior, uint8_t *__restrict__ top1,
-            uint16_t *__restrict__ elev_mask) {
+            uint16_t *__restrict__ elev_mask, const double *__restrict__ table, const uint8_t *__restrict__ table_best) {
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const double *sg = signals + i * LSG_NSIG;
@@ -101,31 +150,22 @@ k_attribute(const __grid_constant__ DevModel m, const double *__restrict__ signa
       if (elev_mask) elev_mask[i] = 0;
       continue;
     }
-    double lp[LSG_NDOM];
-    double mx = -INFINITY;
+    double po[LSG_NDOM];
+    int best;
+    if (TABLE) {
+      const double2 *row = reinterpret_cast<const double2 *>(table + (size_t)elev * LSG_NDOM);
 #pragma unroll
-    for (int d = 0; d < LSG_NDOM; ++d) {
-      double a = m.log_prior[d];
-#pragma unroll
-      for (int s = 0; s < LSG_NSIG; ++s) {
-        if (m.sig_mask >> s & 1) a = __dadd_rn(a, (elev >> s & 1) ? m.log_elev[s][d] : m.log_not[s][d]);
+      for (int d = 0; d < LSG_NDOM / 2; ++d) {
+        const double2 v = __ldg(row + d);
+        po[2 * d] = v.x; po[2 * d + 1] = v.y;
       }
-      a = __dadd_rn(a, m.log_extra[d]);
-      lp[d] = a;
-      mx = a > mx ? a : mx;
+      best = __ldg(table_best + elev);
+    } else {
+      best = posterior_of_mask(m, elev, po);
     }
-    double se = 0.0;
+    double2 *out = reinterpret_cast<double2 *>(posterior + i * LSG_NDOM);
 #pragma unroll
-    for (int d = 0; d < LSG_NDOM; ++d) se = __dadd_rn(se, exp(lp[d] - mx));
-    const double logz = mx + log(se);
-    int best = 0;
-    double bestp = -1.0;
-#pragma unroll
-    for (int d = 0; d < LSG_NDOM; ++d) {
-      const double pd = exp(lp[d] - logz);
-      posterior[i * LSG_NDOM + d] = pd;
-      if (pd > bestp) { bestp = pd; best = d; }
-    }
+    for (int d = 0; d < LSG_NDOM / 2; ++d) out[d] = make_double2(po[2 * d], po[2 * d + 1]);
     top1[i] = (uint8_t)best;
     if (elev_mask) elev_mask[i] = (uint16_t)elev;
   }
@@ -232,12 +272,29 @@ int lsg_launch_incident_features(lsg_ctx *ctx, const double *span_attr, const ui
   return 0;
 }
 
+constexpr size_t AT_TABLE_MIN = 1u << 16;   // incidents from which the mask table pays for its 4096-row build
+
 int lsg_launch_attribute(lsg_ctx *ctx, const double *signals, const uint8_t *has_signals, const uint8_t *rule_label, size_t n,
                          double *posterior, uint8_t *top1, uint16_t *elev_mask) {
   if (n == 0) return 0;
   ProfScope ps(ctx, PK_ATTRIBUTE);
-  k_attribute<<<grid_for(ctx, n, 128, 16), 128, 0, ctx->stream>>>(ctx->model, signals, has_signals, rule_label, n, posterior,
-                                                                   top1, elev_mask);
+  static const bool no_table = getenv("LSG_ATTRIBUTE_DIRECT") != nullptr;   // comparison knob: always the per-incident form
+  if (n >= AT_TABLE_MIN && !no_table) {
+    void *tv = nullptr;
+    LSG_TRY(lsg_ws(ctx, WS_MODEL_TABLE, (size_t)AT_MASKS * (LSG_NDOM * sizeof(double) + 1), &tv));
+    double *table = (double *)tv;
+    uint8_t *best = (uint8_t *)(table + (size_t)AT_MASKS * LSG_NDOM);
+    if (!ctx->model_table_valid) {
+      k_attribute_table<<<AT_MASKS / 128, 128, 0, ctx->stream>>>(ctx->model, table, best);
+      LSG_LAUNCH_CHECK(ctx);
+      ctx->model_table_valid = true;
+    }
+    k_attribute<true><<<grid_for(ctx, n, 128, 16), 128, 0, ctx->stream>>>(ctx->model, signals, has_signals, rule_label, n, posterior,
+                                                                         top1, elev_mask, table, best);
+  } else {
+    k_attribute<false><<<grid_for(ctx, n, 128, 16), 128, 0, ctx->stream>>>(ctx->model, signals, has_signals, rule_label, n,
+                                                                          posterior, top1, elev_mask, nullptr, nullptr);
+  }
   LSG_LAUNCH_CHECK(ctx);
   return 0;
 }

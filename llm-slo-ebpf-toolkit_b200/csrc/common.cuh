@@ -58,6 +58,7 @@ enum {
   WS_BK_SUPER,       // two-level partition: super-bucket cursors
   WS_TILES,          // slab join: tile list
   WS_EV_WIDE,        // events widened from the 24-byte upload form
+  WS_MODEL_TABLE,    // attribution: posteriors and label of every elevated-signal mask under the current model
   WS_IN5,            // host-API staging: feature output
   WS_PIPE,           // first of 2 x PIPE_BUFS staging buffers of the double-buffered host pipeline
   WS_PIPE_END = WS_PIPE + 2 * 20 - 1,
@@ -133,6 +134,7 @@ struct lsg_ctx {
   size_t pinned_cap = 0;
   DevModel model;
   bool model_set = false;
+  bool model_table_valid = false;   // WS_MODEL_TABLE matches `model`
   KeySpec last_key = {};   // key layout of the most recent event sort (diagnostics)
   int join_path = -1;      // -1: LSG_JOIN_PATH decides (default perm), 0: permutation sort + gathering join, 1: bucket partition + slab join
 };
