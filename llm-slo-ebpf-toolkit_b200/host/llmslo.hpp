@@ -11,6 +11,7 @@
 // GPU the first call throws.
 #pragma once
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <map>
@@ -342,6 +343,7 @@ struct Correlator {   // correlator.go:13-17
   ProcessedBatch run(const std::vector<SpanRecord> &spans, const std::vector<correlation::SignalRef> &signals, bool decompose) const {
     ProcessedBatch out;
     if (spans.empty()) return out;
+    const auto t_begin = std::chrono::steady_clock::now();
     const int fanout = MaxJoinFanout > 0 ? MaxJoinFanout : 3;
     detail::Interner in;
     std::vector<lsg_span> sp;
@@ -364,9 +366,11 @@ struct Correlator {   // correlator.go:13-17
     std::vector<uint8_t> ct(spans.size() * fanout);
     std::vector<double> attr(spans.size() * LSG_NSIG), conf(spans.size()), retr(spans.size());
     lsg_debug dbg;
+    const auto t_packed = std::chrono::steady_clock::now();
     Context::check(lsg_process_batch(Context::get(), sp.data(), sp.size(), ev.data(), ev.size(), idents.data(), idents.size(),
                                      (int64_t)WindowMS * Millisecond, EnrichmentThreshold, fanout, any_base ? base.data() : nullptr,
                                      ce.data(), ct.data(), attr.data(), conf.data(), retr.data(), nullptr, &dbg));
+    const auto t_gpu = std::chrono::steady_clock::now();
     for (size_t i = 0; i < spans.size(); ++i) {
       SpanRecord r = spans[i];
       for (int k = 0; k < LSG_NSIG; ++k)
@@ -381,7 +385,18 @@ struct Correlator {   // correlator.go:13-17
       out.Spans.push_back(std::move(r));
     }
     out.Debug = DebugStats{(int64_t)dbg.unmatched, (int64_t)dbg.low_confidence, (int64_t)dbg.fanout_dropped, (int64_t)dbg.unsupported_type};
+    // where a call from the string signatures spends its time (read by host_tests --time)
+    const auto t_end = std::chrono::steady_clock::now();
+    auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    last_timing() = Timing{ms(t_begin, t_packed), ms(t_packed, t_gpu), ms(t_gpu, t_end)};
     return out;
+  }
+
+ public:
+  struct Timing { double intern_ms, library_ms, rebuild_ms; };   // strings -> records | lsg_process_batch | outputs -> maps
+  static Timing &last_timing() {
+    static Timing t{0, 0, 0};
+    return t;
   }
 };
 inline Correlator New() { return Correlator{}; }   // correlator.go:41-47

@@ -391,6 +391,18 @@ def test_full_c2_properties(ctx):
     assert c.debug.as_tuple() == j["debug"].as_tuple()
     assert c.candidates == int(j["n_cand"].sum())
     assert np.array_equal(cand, j["cand_event"]) and np.array_equal(tier, j["cand_tier"])
+    # ... and everything downstream of the join at full size: enriched attributes, per-incident maxima, labels,
+    # posteriors (1e-6), the confusion block
+    attr_full = d.host("attr", np.float64, (ns, A.NSIG))
+    assert np.array_equal(attr_full, j["attr"], equal_nan=True)
+    assert np.array_equal(d.host("conf", np.float64)[:ns], j["conf"])
+    osig = O.incident_features(j["attr"], w["spans"]["incident"], ni)
+    assert np.array_equal(d.host("inc_signals", np.float64, (ni, A.NSIG)), osig, equal_nan=True)
+    opost, otop1, _ = O.attribute(O.default_model(), osig)
+    assert np.array_equal(d.host("top1", np.uint8)[:ni], otop1)
+    assert np.allclose(d.host("posterior", np.float64, (ni, A.NDOM)), opost, rtol=1e-6, atol=0, equal_nan=True)
+    oconf = O.confusion(w["inc_actual"], otop1, w["inc_expected"], w["inc_expected_n"], opost, 0.10, 0.01)
+    assert bytes(c.confusion) == bytes(oconf)
     # sampled join groups, exact
     sp, ids = d.host("spans", A.SPAN_DTYPE), d.host("idents", A.IDENT_DTYPE)
     attr = d.host("attr", np.float64, (ns, A.NSIG))
