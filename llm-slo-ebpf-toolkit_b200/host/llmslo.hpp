@@ -97,21 +97,34 @@ class Interner {
   template <class Rec>
   uint32_t ident(const Rec &r) {
     const uint32_t pod = id(pod_, r.Pod), node = id(node_, r.Node), svc = id(svc_, r.Service);
-    const std::string key = std::to_string(pod) + "/" + std::to_string(node) + "/" + std::to_string(svc);
+    // a batch has few distinct identities and consecutive records often repeat the previous one: the row of the last
+    // triple is kept, everything else is integer-keyed (no strings are built per record)
+    if (have_last_ && pod == last_.pod && node == last_.node && svc == last_.service) return last_row_;
+    const Triple key{pod, node, svc};
     auto it = rows_.find(key);
-    if (it != rows_.end()) return it->second;
-    const uint32_t row = (uint32_t)idents_.size();
-    rows_[key] = row;
-    idents_.push_back(lsg_ident{pod, node, svc, 0});
-    parent_.push_back(row);
-    if (pod) link(by_pod_, std::to_string(pod), row);
-    if (node && svc) link(by_sn_, std::to_string(svc) + "@" + std::to_string(node), row);
+    uint32_t row;
+    if (it != rows_.end()) {
+      row = it->second;
+    } else {
+      row = (uint32_t)idents_.size();
+      rows_.emplace(key, row);
+      idents_.push_back(lsg_ident{pod, node, svc, 0});
+      parent_.push_back(row);
+      if (pod) link(by_pod_, (uint64_t)pod, row);
+      if (node && svc) link(by_sn_, ((uint64_t)svc << 32) | node, row);
+    }
+    last_ = lsg_ident{pod, node, svc, 0}; last_row_ = row; have_last_ = true;
     return row;
   }
   uint32_t trace(const std::string &t, uint32_t row) {
     const uint32_t tid = id(trace_, t);
     if (tid >= (1u << LSG_TRACE_BITS)) throw std::runtime_error("more than 2^28 distinct trace ids in one batch");
-    if (tid) link(by_trace_, std::to_string(tid), row);
+    if (tid) {   // first row seen for a trace id, then union with every later one
+      if (tid >= trace_row_.size()) trace_row_.resize((size_t)tid + 1024, 0xffffffffu);
+      uint32_t &first = trace_row_[tid];
+      if (first == 0xffffffffu) first = row;
+      else if (first != row) unite(first, row);
+    }
     return tid;
   }
   uint32_t conn(const std::string &c) { return id(conn_, c); }
@@ -143,13 +156,32 @@ class Interner {
     while (parent_[x] != x) x = parent_[x] = parent_[parent_[x]];
     return x;
   }
-  void link(Dict &d, const std::string &key, uint32_t row) {
-    auto it = d.find(key);
-    if (it == d.end()) { d[key] = row; return; }
-    const uint32_t a = find(it->second), b = find(row);
+  void unite(uint32_t x, uint32_t y) {
+    const uint32_t a = find(x), b = find(y);
     if (a != b) parent_[std::max(a, b)] = std::min(a, b);
   }
-  Dict trace_, pod_, node_, svc_, conn_, rows_, by_pod_, by_sn_, by_trace_;
+  void link(std::unordered_map<uint64_t, uint32_t> &d, uint64_t key, uint32_t row) {
+    auto it = d.find(key);
+    if (it == d.end()) { d.emplace(key, row); return; }
+    unite(it->second, row);
+  }
+  struct Triple {
+    uint32_t pod, node, service;
+    bool operator==(const Triple &o) const { return pod == o.pod && node == o.node && service == o.service; }
+  };
+  struct TripleHash {
+    size_t operator()(const Triple &t) const {
+      uint64_t h = ((uint64_t)t.pod << 32 | t.node) * 0x9e3779b97f4a7c15ull;
+      return (size_t)((h ^ (h >> 29)) + t.service * 0xbf58476d1ce4e5b9ull);
+    }
+  };
+  Dict trace_, pod_, node_, svc_, conn_;
+  std::unordered_map<Triple, uint32_t, TripleHash> rows_;
+  std::unordered_map<uint64_t, uint32_t> by_pod_, by_sn_;
+  std::vector<uint32_t> trace_row_;
+  lsg_ident last_{0, 0, 0, 0};
+  uint32_t last_row_ = 0;
+  bool have_last_ = false;
   std::vector<lsg_ident> idents_;
   std::vector<uint32_t> parent_;
 };
