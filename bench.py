@@ -128,6 +128,9 @@ def workload_cfg(name, rank, world):
     if name == "c2g1":   # C2's size with every pod in ONE join group: what a trace id that spans all pods does to the grouping
         return synth.config(10_000_000, 1_000_000, 64, 64, 64, 10, 0, rank=rank, world=world), \
             "C2 size, one join group: 10M events x 1M spans, 64 pods in a single group (every span's window exceeds a tile)"
+    if name == "c2fifth":   # C2's density at 1/5 of its size: the 64 MB of event records stay in L2 (what the join costs without DRAM)
+        return synth.config(2_000_000, 200_000, 64, 8, 2, 10, 0, horizon_ns=720 * SECOND, rank=rank, world=world), \
+            "C2/5: 2M events x 200k spans at C2's density (event records L2-resident)"
     if name == "small":
         return synth.config(1_000_000, 100_000, 64, 8, 2, 10, 0, horizon_ns=360 * SECOND, rank=rank, world=world), \
             "C2/10: 1M events x 100k spans (smoke-sized)"

@@ -43,9 +43,28 @@
 
 namespace {
 
-constexpr int JT_THREADS = 256;
+// Shape of the tile kernel.  The macros exist for scratch/build_variant.sh (the same library with other constants, to
+// measure them); what was measured on C2 / C3, join ms (profiles/r02_summary.md):
+//   256 threads, 1792 events, 48 notes, 3 CTAs/SM   0.600 / 72.3     (round 1's choice)
+//   256 threads, 1920 events, 32 notes, 3 CTAs/SM   0.600 / 68.0     <- the halo (outer window) is a smaller share of a tile
+//   256 threads, 2048 events, 24 notes, 3 CTAs/SM   0.604 / 67.3
+//   256 threads, 2816 events, 2 CTAs/SM             0.700 / 74.7
+//   256 threads, 1152 events, 4 CTAs/SM (64 regs)   0.699
+//   128 threads, 1152 events, 5 CTAs/SM             0.668
+//   128 threads,  896 events, 6 CTAs/SM             0.851
+// More resident CTAs do not pay for a smaller tile: every tile gathers the +-window halo of its spans again.
+#ifndef LSG_JT_THREADS
+#define LSG_JT_THREADS 256
+#endif
+#ifndef LSG_TM_CAP
+#define LSG_TM_CAP 1920
+#endif
+#ifndef LSG_JT_OCC
+#define LSG_JT_OCC 3
+#endif
+constexpr int JT_THREADS = LSG_JT_THREADS;
 constexpr int JT_WARPS = JT_THREADS / 32;
-constexpr int JT_CH = 128;     // spans per chunk
+constexpr int JT_CH = JT_THREADS / 2;     // spans per chunk: two threads per span
 
 struct JoinParams {
   const lsg_span *spans;
@@ -458,10 +477,13 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
 // A match is only noted — two bytes (tier, tile offset) in the span's list — and the lists are ordered
 // afterwards in registers, when every lane is doing the same thing.  A span whose list overflows (or whose range
 // does not fit a tile) is left to k_join_big.
-constexpr int TM_CAP = 1792;    // events per tile (28 B each; three CTAs per SM)
-constexpr int TM_LIST = 48;     // noted candidates per span
+constexpr int TM_CAP = LSG_TM_CAP;    // events per tile (28 B each; three CTAs per SM)
+#ifndef LSG_TM_LIST
+#define LSG_TM_LIST 32
+#endif
+constexpr int TM_LIST = LSG_TM_LIST;     // noted candidates per span
 constexpr int TM_MAX_F = 8;      // largest fanout the tile kernel keeps in registers
-constexpr int TM_HASH = 256;    // hash slots for the chunk's span trace ids (<= 128 keys)
+constexpr int TM_HASH = JT_THREADS;    // hash slots for the chunk's span trace ids (<= 128 keys)
 constexpr uint16_t TM_END = 0xffffu;
 
 template <int F>
@@ -509,12 +531,12 @@ struct TileSmem {
   uint64_t bar;
 };
 
-__device__ __forceinline__ uint32_t trace_slot(uint32_t tr) { return (tr * 2654435761u) >> 24; }   // 8 bits
+__device__ __forceinline__ uint32_t trace_slot(uint32_t tr) { return (tr * 2654435761u) >> (TM_HASH == 256 ? 24 : TM_HASH == 128 ? 25 : 23); }
 
 // FUSED: there is no sorted copy of the events; the CTA gathers its tile's records through the permutation itself
 // (random 32-byte reads, issued four deep per thread), writing the columns and the (pod, class) words in one go.
 template <int F, bool T32, bool FUSED>
-__global__ void __launch_bounds__(JT_THREADS, 3)
+__global__ void __launch_bounds__(JT_THREADS, LSG_JT_OCC)
 k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TileSmem &sm = *reinterpret_cast<TileSmem *>(smem_raw);
@@ -1051,6 +1073,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
     int occ = 1;
     LSG_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, JT_THREADS, smem));
     if (occ < 1) occ = 1;
+    static const bool say = getenv("LSG_DEBUG_OCC") != nullptr;
+    if (say) fprintf(stderr, "k_join_tiles: %d threads, %zu B of shared memory, %d CTAs per SM\n", JT_THREADS, smem, occ);
     size_t blocks = n_chunks, cap = (size_t)ctx->sm_count * occ;
     if (blocks > cap) blocks = cap;
     kernel<<<(unsigned)blocks, JT_THREADS, smem, ctx->stream>>>(p, big_list, big_count);

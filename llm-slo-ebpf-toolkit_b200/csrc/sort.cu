@@ -28,8 +28,7 @@
 
 namespace {
 
-constexpr int RADIX_BITS = 8;
-constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int RADIX_MAX_BITS = 10;   // widest digit of a radix pass
 constexpr int SORT_BLOCK = 512;
 constexpr int SORT_IPT = 16;
 constexpr int SORT_TILE = SORT_BLOCK * SORT_IPT;  // 8192 keys per CTA
@@ -200,12 +199,15 @@ k_span_keys(const lsg_span *__restrict__ spans, size_t n, const lsg_ident *__res
 }
 
 // ---- one radix pass ------------------------------------------------------------------------------
-// lanes of the warp whose 8-bit digit equals this lane's: eight ballots instead of match.any, which is
-// issued through the (slow, shared) MIO queue on sm_100 and throttled both radix kernels
+// The digit is BITS wide (8, 9 or 10): the passes share the key's bits evenly, so 17-20 bits take two passes and
+// 25-30 bits three (with 8-bit digits alone 29 bits would take four, each a read and a write of every pair).
+// lanes of the warp whose digit equals this lane's: BITS ballots instead of match.any, which is issued through the
+// (slow, shared) MIO queue on sm_100 and throttled both radix kernels
+template <int BITS>
 __device__ __forceinline__ unsigned peers_of_digit(const unsigned d) {
   unsigned peers = 0xffffffffu;
 #pragma unroll
-  for (int b = 0; b < RADIX_BITS; ++b) {
+  for (int b = 0; b < BITS; ++b) {
     const bool bit = (d >> b) & 1u;
     const unsigned bal = __ballot_sync(0xffffffffu, bit);
     peers &= bit ? bal : ~bal;
@@ -213,15 +215,19 @@ __device__ __forceinline__ unsigned peers_of_digit(const unsigned d) {
   return peers;
 }
 
-template <typename KeyT>
+// Per-tile digit counts.  Shared-memory atomics on four copies of the counter row (a warp whose 32 keys all carry one
+// digit adds 32 at once: the top digit of a batch with few groups); the ballot ranking of the scatter is not needed to
+// count, and cost 3.6 ms per pass over 10^9 keys against 0.7 ms for the read.
+template <typename KeyT, int BITS>
 __global__ void __launch_bounds__(SORT_BLOCK)
 k_radix_hist(const KeyT *__restrict__ keys, size_t n, int shift, uint32_t *__restrict__ tile_hist, uint32_t n_tiles) {
-  __shared__ uint32_t s_hist[SORT_NW][RADIX];   // one counter row per warp: leaders update without atomics
-  for (int i = threadIdx.x; i < SORT_NW * RADIX; i += SORT_BLOCK) (&s_hist[0][0])[i] = 0;
+  constexpr int R = 1 << BITS;
+  __shared__ uint32_t s_hist[4][R];
+  for (int i = threadIdx.x; i < 4 * R; i += SORT_BLOCK) (&s_hist[0][0])[i] = 0;
   __syncthreads();
   const size_t base = (size_t)blockIdx.x * SORT_TILE;
-  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint32_t *mine = s_hist[warp];
+  const unsigned lane = threadIdx.x & 31;
+  uint32_t *mine = s_hist[(threadIdx.x >> 5) & 3];
   KeyT k[SORT_IPT];
 #pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
@@ -232,18 +238,17 @@ k_radix_hist(const KeyT *__restrict__ keys, size_t n, int shift, uint32_t *__res
   for (int i = 0; i < SORT_IPT; ++i) {
     const size_t pos = base + (size_t)i * SORT_BLOCK + threadIdx.x;
     const bool valid = pos < n;
-    const unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
-    const unsigned peers = peers_of_digit(d) & __ballot_sync(0xffffffffu, valid);
-    if (valid && lane == (unsigned)(__ffs(peers) - 1)) mine[d] += __popc(peers);
-    __syncwarp();
+    const unsigned d = (unsigned)((k[i] >> shift) & (R - 1));
+    const unsigned d0 = __shfl_sync(0xffffffffu, d, 0);
+    if (__all_sync(0xffffffffu, valid && d == d0)) {
+      if (lane == 0) atomicAdd(&mine[d0], 32u);
+    } else if (valid) {
+      atomicAdd(&mine[d], 1u);
+    }
   }
   __syncthreads();
-  for (int d = threadIdx.x; d < RADIX; d += SORT_BLOCK) {
-    uint32_t t = 0;
-#pragma unroll
-    for (int w = 0; w < SORT_NW; ++w) t += s_hist[w][d];
-    tile_hist[(size_t)d * n_tiles + blockIdx.x] = t;
-  }
+  for (int d = threadIdx.x; d < R; d += SORT_BLOCK)
+    tile_hist[(size_t)d * n_tiles + blockIdx.x] = s_hist[0][d] + s_hist[1][d] + s_hist[2][d] + s_hist[3][d];
 }
 
 // exclusive scan of each digit's row over the tiles (in place); one CTA per digit
@@ -282,8 +287,9 @@ k_radix_scan_tiles(uint32_t *__restrict__ tile_hist, uint32_t n_tiles, uint32_t 
   if (threadIdx.x == 0) digit_total[blockIdx.x] = s_carry;
 }
 
-__global__ void __launch_bounds__(RADIX) k_radix_scan_digits(const uint32_t *__restrict__ digit_total, uint32_t *__restrict__ digit_base) {
-  __shared__ uint32_t s_warp[RADIX / 32];
+// exclusive scan of the digit totals: one CTA of as many threads as there are digits (256 .. 1024)
+__global__ void __launch_bounds__(1024) k_radix_scan_digits(const uint32_t *__restrict__ digit_total, uint32_t *__restrict__ digit_base) {
+  __shared__ uint32_t s_warp[32];
   const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t v = digit_total[threadIdx.x], x = v;
   for (int o = 1; o < 32; o <<= 1) {
@@ -297,23 +303,32 @@ __global__ void __launch_bounds__(RADIX) k_radix_scan_digits(const uint32_t *__r
   digit_base[threadIdx.x] = pre + x - v;
 }
 
-template <typename KeyT>
+// shared memory of the scatter: per-warp digit counters (16 bits: a warp ranks 512 items, a tile holds 8192), the
+// digits' tile-local and global bases, and the tile's pairs in digit order
+template <typename KeyT, int BITS>
+constexpr size_t scatter_smem_bytes() {
+  return (size_t)SORT_NW * (1 << BITS) * 2 + (size_t)(1 << BITS) * 8 + 64 * 4 + (size_t)SORT_TILE * 4 + (size_t)SORT_TILE * sizeof(KeyT);
+}
+
+template <typename KeyT, int BITS>
 __global__ void __launch_bounds__(SORT_BLOCK, 2)
 k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ idx_in, KeyT *__restrict__ keys_out,
                 uint32_t *__restrict__ idx_out, size_t n, int shift, const uint32_t *__restrict__ tile_off,
                 const uint32_t *__restrict__ digit_base, uint32_t n_tiles) {
+  constexpr int R = 1 << BITS;
+  constexpr int DPT = R > SORT_BLOCK ? R / SORT_BLOCK : 1;   // digits per thread in the tile-level scan
   extern __shared__ __align__(16) unsigned char smem[];
-  uint32_t *warp_cnt = reinterpret_cast<uint32_t *>(smem);  // [SORT_NW][RADIX]
-  uint32_t *bin_off = warp_cnt + SORT_NW * RADIX;           // [RADIX] first tile-local slot of each digit
-  uint32_t *gbase = bin_off + RADIX;                        // [RADIX] global position of tile-local slot 0, per digit
-  uint32_t *s_scan = gbase + RADIX;                         // [8]
-  uint32_t *s_idx = s_scan + 8;                             // [SORT_TILE]
+  uint32_t *bin_off = reinterpret_cast<uint32_t *>(smem);   // [R] first tile-local slot of each digit
+  uint32_t *gbase = bin_off + R;                            // [R] global position of tile-local slot 0, per digit
+  uint32_t *s_scan = gbase + R;                             // [64]
+  uint32_t *s_idx = s_scan + 64;                            // [SORT_TILE]
   KeyT *s_keys = reinterpret_cast<KeyT *>(s_idx + SORT_TILE);  // [SORT_TILE]
+  uint16_t *warp_cnt = reinterpret_cast<uint16_t *>(s_keys + SORT_TILE);  // [SORT_NW][R]
 
   const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const size_t base = (size_t)blockIdx.x * SORT_TILE;
   const uint32_t count = (uint32_t)min((size_t)SORT_TILE, n - base);
-  for (int i = tid; i < SORT_NW * RADIX; i += SORT_BLOCK) warp_cnt[i] = 0;
+  for (int i = tid; i < SORT_NW * R / 2; i += SORT_BLOCK) reinterpret_cast<uint32_t *>(warp_cnt)[i] = 0;
   __syncthreads();
 
   // warp-striped load: warp w owns tile slots [w*32*IPT, (w+1)*32*IPT), item i of lane l is slot i*32+l
@@ -326,48 +341,62 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
     k[i] = pos < n ? keys_in[pos] : (KeyT)~(KeyT)0;   // padding sorts behind every real key of the tile (stable)
   }
   // stable rank of each item among the items of its warp with the same digit
-  uint32_t *my_cnt = warp_cnt + warp * RADIX;
+  uint16_t *my_cnt = warp_cnt + warp * R;
   const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll
   for (int i = 0; i < SORT_IPT; ++i) {
-    unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
-    unsigned m = peers_of_digit(d);
+    unsigned d = (unsigned)((k[i] >> shift) & (R - 1));
+    unsigned m = peers_of_digit<BITS>(d);
     int leader = __ffs(m) - 1;
     uint32_t old = 0;
     if ((int)lane == leader) {
       old = my_cnt[d];
-      my_cnt[d] = old + __popc(m);
+      my_cnt[d] = (uint16_t)(old + __popc(m));
     }
     old = __shfl_sync(0xffffffffu, old, leader);
     rank[i] = (uint16_t)(old + __popc(m & lt_mask));
     __syncwarp();
   }
   __syncthreads();
-  // per digit: exclusive scan over the warps, then over the digits
-  uint32_t total = 0;
-  if (tid < RADIX) {
-    uint32_t run = 0;
+  // per digit: exclusive scan over the warps, then over the digits (thread t owns digits [t*DPT, (t+1)*DPT))
+  uint32_t tot[DPT];
+  uint32_t mine = 0;
 #pragma unroll
-    for (int w = 0; w < SORT_NW; ++w) {
-      uint32_t c = warp_cnt[w * RADIX + tid];
-      warp_cnt[w * RADIX + tid] = run;
-      run += c;
+  for (int q = 0; q < DPT; ++q) {
+    const unsigned d = tid * DPT + q;
+    tot[q] = 0;
+    if (d < (unsigned)R) {
+      uint32_t run = 0;
+#pragma unroll
+      for (int w = 0; w < SORT_NW; ++w) {
+        const uint32_t c = warp_cnt[w * R + d];
+        warp_cnt[w * R + d] = (uint16_t)run;
+        run += c;
+      }
+      tot[q] = run;
     }
-    total = run;
+    mine += tot[q];
   }
-  uint32_t x = total;
+  uint32_t x = mine;
   for (int o = 1; o < 32; o <<= 1) {
     uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
     if (lane >= (unsigned)o) x += y;
   }
-  if (tid < RADIX && lane == 31) s_scan[warp] = x;
+  if (lane == 31) s_scan[warp] = x;
   __syncthreads();
-  if (tid < RADIX) {
+  {
     uint32_t pre = 0;
     for (unsigned w = 0; w < warp; ++w) pre += s_scan[w];
-    uint32_t excl = pre + x - total;
-    bin_off[tid] = excl;
-    gbase[tid] = digit_base[tid] + tile_off[(size_t)tid * n_tiles + blockIdx.x] - excl;
+    uint32_t excl = pre + x - mine;
+#pragma unroll
+    for (int q = 0; q < DPT; ++q) {
+      const unsigned d = tid * DPT + q;
+      if (d < (unsigned)R) {
+        bin_off[d] = excl;
+        gbase[d] = digit_base[d] + tile_off[(size_t)d * n_tiles + blockIdx.x] - excl;
+        excl += tot[q];
+      }
+    }
   }
   __syncthreads();
   // the payload (input index) is read only now, so that it never sits in registers during the ranking
@@ -375,7 +404,7 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
   for (int i = 0; i < SORT_IPT; ++i) {
     const size_t pos = wbase + (size_t)i * 32 + lane;
     const uint32_t v = pos < n ? (idx_in ? idx_in[pos] : (uint32_t)pos) : 0u;
-    unsigned d = (unsigned)((k[i] >> shift) & (RADIX - 1));
+    unsigned d = (unsigned)((k[i] >> shift) & (R - 1));
     uint32_t lp = bin_off[d] + my_cnt[d] + rank[i];
     s_keys[lp] = k[i];
     s_idx[lp] = v;
@@ -384,7 +413,7 @@ k_radix_scatter(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ i
   // tile is now in digit order in shared memory: runs of equal digits go to consecutive global slots
   for (uint32_t j = tid; j < count; j += SORT_BLOCK) {
     KeyT key = s_keys[j];
-    unsigned d = (unsigned)((key >> shift) & (RADIX - 1));
+    unsigned d = (unsigned)((key >> shift) & (R - 1));
     size_t out = (size_t)gbase[d] + j;
     keys_out[out] = key;
     idx_out[out] = s_idx[j];
@@ -611,10 +640,6 @@ k_scan_apply(uint32_t *__restrict__ data, size_t n, const uint32_t *__restrict__
   }
 }
 
-size_t scatter_smem(size_t key_bytes) {
-  return (size_t)(SORT_NW * RADIX + RADIX + RADIX + 8 + SORT_TILE) * 4 + (size_t)SORT_TILE * key_bytes;
-}
-
 inline unsigned grid_for(lsg_ctx *ctx, size_t n, int block, int per_sm) {
   size_t blocks = (n + block - 1) / block;
   size_t cap = (size_t)ctx->sm_count * per_sm;
@@ -623,43 +648,66 @@ inline unsigned grid_for(lsg_ctx *ctx, size_t n, int block, int per_sm) {
   return (unsigned)blocks;
 }
 
+// one pass: histogram, scans, scatter
+template <typename KeyT, int BITS>
+int radix_pass(lsg_ctx *ctx, const KeyT *kin, const uint32_t *iin, KeyT *kout, uint32_t *iout, size_t n, int shift, uint32_t n_tiles,
+               uint32_t *tile_hist, uint32_t *digit_total, uint32_t *digit_base, int prof_base) {
+  constexpr int R = 1 << BITS;
+  constexpr size_t smem = scatter_smem_bytes<KeyT, BITS>();
+  LSG_CUDA(ctx, cudaFuncSetAttribute(k_radix_scatter<KeyT, BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {
+    ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_HIST);
+    k_radix_hist<KeyT, BITS><<<n_tiles, SORT_BLOCK, 0, ctx->stream>>>(kin, n, shift, tile_hist, n_tiles);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  {
+    ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCAN);
+    k_radix_scan_tiles<<<R, 1024, 0, ctx->stream>>>(tile_hist, n_tiles, digit_total);
+    LSG_LAUNCH_CHECK(ctx);
+    k_radix_scan_digits<<<1, R, 0, ctx->stream>>>(digit_total, digit_base);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  {
+    ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCATTER);
+    k_radix_scatter<KeyT, BITS><<<n_tiles, SORT_BLOCK, smem, ctx->stream>>>(kin, iin, kout, iout, n, shift, tile_hist, digit_base, n_tiles);
+    LSG_LAUNCH_CHECK(ctx);
+  }
+  return 0;
+}
+
+// how the key's bits are shared between the passes: as few passes as 10-bit digits allow, digits of equal width (the
+// last one takes what is left), never narrower than 8 bits unless the key itself is
+inline int radix_plan(int bits, int *width) {
+  if (bits < 1) bits = 1;
+  const int passes = (bits + RADIX_MAX_BITS - 1) / RADIX_MAX_BITS;
+  int w = (bits + passes - 1) / passes;
+  if (w < 8) w = 8;
+  *width = w;
+  return (bits + w - 1) / w;
+}
+
 // LSD radix sort of (key, idx) pairs over key bits [0, bits).  Result pointers are returned (ping or pong).
 template <typename KeyT>
 int radix_sort_pairs(lsg_ctx *ctx, KeyT *keys_a, KeyT *keys_b, uint32_t *idx_a, uint32_t *idx_b, size_t n, int bits,
                      int slot_hist, KeyT **keys_out, uint32_t **idx_out, int prof_base = -1) {
   const uint32_t n_tiles = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
+  int width = 8;
+  const int passes = radix_plan(bits, &width);
+  const size_t R = (size_t)1 << width;
   void *hist_v = nullptr;
-  LSG_TRY(lsg_ws(ctx, slot_hist, ((size_t)RADIX * n_tiles + 2 * RADIX) * 4, &hist_v));
+  LSG_TRY(lsg_ws(ctx, slot_hist, (R * n_tiles + 2 * R) * 4, &hist_v));
   uint32_t *tile_hist = (uint32_t *)hist_v;
-  uint32_t *digit_total = tile_hist + (size_t)RADIX * n_tiles;
-  uint32_t *digit_base = digit_total + RADIX;
-  const size_t smem = scatter_smem(sizeof(KeyT));
-  LSG_CUDA(ctx, cudaFuncSetAttribute(k_radix_scatter<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
+  uint32_t *digit_total = tile_hist + R * n_tiles;
+  uint32_t *digit_base = digit_total + R;
   KeyT *kin = keys_a, *kout = keys_b;
   uint32_t *iin = nullptr, *iout = idx_b;  // first pass: identity indices
   uint32_t *ia = idx_a, *ib = idx_b;
   for (int p = 0; p < passes; ++p) {
-    const int shift = p * RADIX_BITS;
-    {
-      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_HIST);
-      k_radix_hist<KeyT><<<n_tiles, SORT_BLOCK, 0, ctx->stream>>>(kin, n, shift, tile_hist, n_tiles);
-      LSG_LAUNCH_CHECK(ctx);
-    }
-    {
-      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCAN);
-      k_radix_scan_tiles<<<RADIX, 1024, 0, ctx->stream>>>(tile_hist, n_tiles, digit_total);
-      LSG_LAUNCH_CHECK(ctx);
-      k_radix_scan_digits<<<1, RADIX, 0, ctx->stream>>>(digit_total, digit_base);
-      LSG_LAUNCH_CHECK(ctx);
-    }
+    const int shift = p * width;
     iout = (p & 1) ? ia : ib;
-    {
-      ProfScope ps(ctx, prof_base >= 0 ? prof_base : PK_SCATTER);
-      k_radix_scatter<KeyT><<<n_tiles, SORT_BLOCK, smem, ctx->stream>>>(kin, iin, kout, iout, n, shift, tile_hist, digit_base,
-                                                                     n_tiles);
-      LSG_LAUNCH_CHECK(ctx);
-    }
+    if (width == 8) LSG_TRY((radix_pass<KeyT, 8>(ctx, kin, iin, kout, iout, n, shift, n_tiles, tile_hist, digit_total, digit_base, prof_base)));
+    else if (width == 9) LSG_TRY((radix_pass<KeyT, 9>(ctx, kin, iin, kout, iout, n, shift, n_tiles, tile_hist, digit_total, digit_base, prof_base)));
+    else LSG_TRY((radix_pass<KeyT, 10>(ctx, kin, iin, kout, iout, n, shift, n_tiles, tile_hist, digit_total, digit_base, prof_base)));
     KeyT *t = kin; kin = kout; kout = t;
     iin = iout;
   }
@@ -802,7 +850,8 @@ int lsg_sort_events_finish(lsg_ctx *ctx, const lsg_event *events, size_t n, cons
     LSG_LAUNCH_CHECK(ctx);
     return 0;
   };
-  if (allow_counting && ks.shift != 0 && ks.dead <= COUNTING_MAX_KEYS) {
+  static const uint64_t counting_max = getenv("LSG_COUNTING_MAX_BITS") ? (uint64_t)1 << atoi(getenv("LSG_COUNTING_MAX_BITS")) : COUNTING_MAX_KEYS;
+  if (allow_counting && ks.shift != 0 && ks.dead <= counting_max) {
     const size_t n_keys = (size_t)ks.dead + 1;   // live keys are < dead; one extra entry so that bins[k + 1] always exists
     void *bv, *sv, *pv, *kv;
     LSG_TRY(lsg_ws(ctx, WS_BINS, (n_keys + SCAN_TILE) * 4, &bv));

@@ -1,5 +1,6 @@
-"""Aggregate an ncu source-page export (cuda,sass correlated) by source line / by phase markers of join_slab.cuh.
-usage: ncu -i X.ncu-rep --page source --csv --print-source cuda,sass > src.csv; python scratch/ncu_phases.py src.csv [top]"""
+"""Aggregate an ncu source-page export (cuda,sass correlated) by source line / by the `// ---- ` phase markers of one file.
+usage: ncu -i X.ncu-rep --page source --csv --print-source cuda,sass > src.csv; python scratch/ncu_phases.py src.csv [top] [file]
+(file: join_slab.cuh by default, join.cu for the default join)"""
 import collections
 import csv
 import re
@@ -8,7 +9,8 @@ import sys
 path = sys.argv[1]
 top_n = int(sys.argv[2]) if len(sys.argv) > 2 else 30
 rows = list(csv.reader(open(path)))
-src = open("llm-slo-ebpf-toolkit_b200/csrc/join_slab.cuh").read().splitlines()
+main_file = sys.argv[3] if len(sys.argv) > 3 else "join_slab.cuh"
+src = open("llm-slo-ebpf-toolkit_b200/csrc/" + main_file).read().splitlines()
 marks = [(i + 1, ln.strip()[8:60]) for i, ln in enumerate(src) if re.match(r"\s*// ---- ", ln)]
 cur, hdr = None, None
 line_agg = collections.defaultdict(lambda: [0, 0, 0, ""])
@@ -36,7 +38,7 @@ for r in rows:
         continue
     a = line_agg[(cur, line)]
     a[0] += inst; a[1] += thr; a[2] += smp; a[3] = r[1][:80]
-    if cur == "join_slab.cuh":
+    if cur == main_file:
         ph = "start"
         for ln, name in marks:
             if ln <= line:
