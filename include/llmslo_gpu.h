@@ -167,7 +167,9 @@ uint64_t lsg_launch_count(const lsg_ctx *ctx);
 /* Which of the two implementations of the sort + join stages lsg_process_batch / lsg_pipeline take (same results):
  * 0 = permutation sort (counting / radix) + a join that gathers its tiles through the permutation (default),
  * 1 = bucket partition of the records + slab join on contiguous tiles, -1 = the LSG_JOIN_PATH environment variable
- * ("slab" or "perm") decides.  A tuning knob with no reference counterpart. */
+ * ("slab" or "perm") decides.  Path 0 picks one of two forms of its tile kernel by the batch's density (a sliding tile
+ * when a chunk of spans reaches more events than one tile holds, fixed chunks otherwise); 2 and 3 are path 0 with the
+ * sliding / the fixed form forced (tests, measurements).  A tuning knob with no reference counterpart. */
 int lsg_set_join_path(lsg_ctx *ctx, int path);
 /* bytes of device workspace currently held */
 size_t lsg_workspace_bytes(const lsg_ctx *ctx);

@@ -362,7 +362,7 @@ int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_sh
 
 const char *lsg_last_error(const lsg_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 int lsg_set_join_path(lsg_ctx *ctx, int path) {
-  if (!ctx || path < -1 || path > 1) return LSG_ERR_INVALID;
+  if (!ctx || path < -1 || path > 3) return LSG_ERR_INVALID;
   ctx->join_path = path;
   return 0;
 }

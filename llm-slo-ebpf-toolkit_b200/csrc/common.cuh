@@ -136,7 +136,8 @@ struct lsg_ctx {
   bool model_set = false;
   bool model_table_valid = false;   // WS_MODEL_TABLE matches `model`
   KeySpec last_key = {};   // key layout of the most recent event sort (diagnostics)
-  int join_path = -1;      // -1: LSG_JOIN_PATH decides (default perm), 0: permutation sort + gathering join, 1: bucket partition + slab join
+  int join_path = -1;      // -1: LSG_JOIN_PATH decides (default perm), 0: permutation sort + gathering join, 1: bucket partition + slab join,
+                           // 2 / 3: as 0 with the sliding-tile / the fixed-chunk form of the tile kernel forced
 };
 
 int lsg_fail(lsg_ctx *ctx, int code, const char *fmt, ...);

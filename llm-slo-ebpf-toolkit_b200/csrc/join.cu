@@ -62,6 +62,9 @@ namespace {
 #ifndef LSG_JT_OCC
 #define LSG_JT_OCC 3
 #endif
+#ifndef LSG_JT_DEPTH
+#define LSG_JT_DEPTH 2   // records a thread of the loader has in flight (measured on C2 / C3: 1: 0.608 / 67.0, 2: 0.592 / 66.8, 4: 0.605 / 68.6, 8: 0.625 / 70.1)
+#endif
 constexpr int JT_THREADS = LSG_JT_THREADS;
 constexpr int JT_WARPS = JT_THREADS / 32;
 constexpr int JT_CH = JT_THREADS / 2;     // spans per chunk: two threads per span
@@ -643,16 +646,16 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           src[u] = o < live_end ? __ldg(p.ev_perm + A + o) : 0xffffffffu;
         }
 #pragma unroll
-        for (int ub = 0; ub < PER; ub += 4) {
-          U8 r[4];
+        for (int ub = 0; ub < PER; ub += LSG_JT_DEPTH) {
+          U8 r[LSG_JT_DEPTH];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < LSG_JT_DEPTH; ++u) {
             r[u].a = make_uint4(0, 0, 0, 0);
             r[u].b = make_uint4(0xffffffffu, 0, 0, 0);   // padding: an identity row no table has
             if (ub + u < PER && src[ub + u] != 0xffffffffu) r[u] = ld_nc_v8(p.events_in + src[ub + u]);
           }
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < LSG_JT_DEPTH; ++u) {
             const uint32_t o = tid + (ub + u) * JT_THREADS;
             if (ub + u >= PER || o >= count) continue;
             const uint32_t row = r[u].b.x;
@@ -923,6 +926,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
   if (tid < 5 && sm.cnt[tid]) atomicAdd(&p.counters[tid], sm.cnt[tid]);
 }
 
+#include "join_ring.cuh"
+
 __global__ void k_list_all_spans(uint32_t *__restrict__ big_list, unsigned int *__restrict__ big_count, uint32_t n) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) big_list[i] = i;
   if (blockIdx.x == 0 && threadIdx.x == 0) *big_count = n;
@@ -1087,7 +1092,34 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   const bool fused = a.ev.col.ts == nullptr;
   if (fused && !a.events_in && a.ev.n != 0)
     return lsg_fail(ctx, LSG_ERR_INVALID, "join without sorted columns needs the input records");
-  if (a.fanout <= 3) {
+  // Which form of the fused tile kernel.  Measured (profiles/r02_summary.md), join ms, fixed chunks / sliding tile:
+  // C2 (10 events per span) 0.590 / 0.619, C3 (20 events per span) 66.8 / 52.3.  With few events per span a chunk of
+  // 128 spans fits one tile and the halo it gathers again is in L2 already (the CTA next door has just fetched it);
+  // with many, every chunk needs two tiles and the halo is most of the second.  So: sliding tile when 128 spans reach
+  // more events than a fixed tile holds after its halo (~13 events per span), fixed chunks below.
+  // lsg_set_join_path 2 / 3 or LSG_JOIN_RING=1 / 0 force one form.
+  static const int ring_force = getenv("LSG_JOIN_RING") ? atoi(getenv("LSG_JOIN_RING")) : -1;
+  bool ring_env = a.ev.n >= 13 * a.n_spans;
+  if (ring_force >= 0) ring_env = ring_force != 0;
+  if (ctx->join_path == 2) ring_env = true;
+  if (ctx->join_path == 3) ring_env = false;
+  auto launch_ring = [&](auto kernel) -> int {
+    const size_t rsmem = sizeof(RingSmem);
+    LSG_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
+    int occ = 1;
+    LSG_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, JT_THREADS, rsmem));
+    if (occ < 1) occ = 1;
+    static const bool say = getenv("LSG_DEBUG_OCC") != nullptr;
+    if (say) fprintf(stderr, "k_join_ring: %d threads, %zu B of shared memory, %d CTAs per SM\n", JT_THREADS, rsmem, occ);
+    size_t blocks = n_chunks, cap = (size_t)ctx->sm_count * occ;
+    if (blocks > cap) blocks = cap;
+    kernel<<<(unsigned)blocks, JT_THREADS, rsmem, ctx->stream>>>(p, big_list, big_count, (unsigned long long *)(a.counters + 7));
+    return 0;
+  };
+  if (fused && ring_env && a.fanout <= TM_MAX_F) {
+    if (a.fanout <= 3) { if (t32) LSG_TRY(launch_ring(k_join_ring<3, true>)); else LSG_TRY(launch_ring(k_join_ring<3, false>)); }
+    else { if (t32) LSG_TRY(launch_ring(k_join_ring<TM_MAX_F, true>)); else LSG_TRY(launch_ring(k_join_ring<TM_MAX_F, false>)); }
+  } else if (a.fanout <= 3) {
     if (fused) { if (t32) LSG_TRY(launch(k_join_tiles<3, true, true>)); else LSG_TRY(launch(k_join_tiles<3, false, true>)); }
     else { if (t32) LSG_TRY(launch(k_join_tiles<3, true, false>)); else LSG_TRY(launch(k_join_tiles<3, false, false>)); }
   } else if (a.fanout <= TM_MAX_F) {
