@@ -444,6 +444,8 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
             sass = ({"join": "k_join_slab", "bucket_scatter": "k_bucket_scatter", "bucket_count": "k_bucket_count"} if slab else
                     {"join": "k_join_tiles", "radix_hist": "k_count_keys" if "event_keys" not in per_kernel else "k_radix_hist",
                      "radix_scatter": "k_place_events" if "event_keys" not in per_kernel else "k_radix_scatter"}).get(dom)
+            if sass == "k_join_tiles" and sass not in capj["kernels"] and "k_join_ring" in capj["kernels"]:
+                sass = "k_join_ring"   # dense batches take the sliding-tile form of the kernel
             if sass in capj["kernels"]:
                 traffic = capj["kernels"][sass]["dram_bytes_per_launch"]
                 cap_src = "ncu --set full capture at commit %s (profiles/r02_ncu_traffic_%s.json)" % (capj.get("commit", "?"), name)

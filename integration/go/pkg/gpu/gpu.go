@@ -357,7 +357,8 @@ func PackEvents24(events []Event, base int64) (out []Event24, misfit int64) {
 }
 
 // SetJoinPath selects the implementation of the sort + join stages (0 permutation sort + gathering join, 1 bucket
-// partition + slab join, -1 the LSG_JOIN_PATH environment variable decides).
+// partition + slab join, -1 the LSG_JOIN_PATH environment variable decides; 2 / 3 are path 0 with the sliding-tile /
+// the fixed-chunk form of its tile kernel forced instead of chosen by the batch's events per span).
 func (c *Ctx) SetJoinPath(path int) error {
 	defer c.enter()()
 	return c.err(C.lsg_set_join_path(c.h, C.int(path)))

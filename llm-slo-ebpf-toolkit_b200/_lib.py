@@ -284,7 +284,8 @@ class Context:
         return tuple(int(x) for x in out)
 
     def set_join_path(self, path):
-        """0: permutation sort + gathering join (default), 1: bucket partition + slab join, -1: LSG_JOIN_PATH decides."""
+        """0: permutation sort + gathering join (default), 1: bucket partition + slab join, -1: LSG_JOIN_PATH decides;
+        2 / 3: path 0 with the sliding-tile / the fixed-chunk form of its tile kernel forced."""
         self._check(self._lib.lsg_set_join_path(self._h, int(path)))
 
     def profile_enable(self, on=True):

@@ -45,9 +45,9 @@ namespace {
 
 // Shape of the tile kernel.  The macros exist for scratch/build_variant.sh (the same library with other constants, to
 // measure them); what was measured on C2 / C3, join ms (profiles/r02_summary.md):
-//   256 threads, 1792 events, 48 notes, 3 CTAs/SM   0.600 / 72.3     (round 1's choice)
-//   256 threads, 1920 events, 32 notes, 3 CTAs/SM   0.600 / 68.0     <- the halo (outer window) is a smaller share of a tile
-//   256 threads, 2048 events, 24 notes, 3 CTAs/SM   0.604 / 67.3
+//   256 threads, 1792 events, 48 notes, 3 CTAs/SM   0.600 / 72.3     <- (with two records in flight per loader thread: 0.587)
+//   256 threads, 1920 events, 32 notes, 3 CTAs/SM   0.600 / 68.0     (0.592: more spans overflow their note list and are
+//   256 threads, 2048 events, 24 notes, 3 CTAs/SM   0.604 / 67.3      redone by k_join_big, 23 us per step instead of 5)
 //   256 threads, 2816 events, 2 CTAs/SM             0.700 / 74.7
 //   256 threads, 1152 events, 4 CTAs/SM (64 regs)   0.699
 //   128 threads, 1152 events, 5 CTAs/SM             0.668
@@ -57,7 +57,7 @@ namespace {
 #define LSG_JT_THREADS 256
 #endif
 #ifndef LSG_TM_CAP
-#define LSG_TM_CAP 1920
+#define LSG_TM_CAP 1792
 #endif
 #ifndef LSG_JT_OCC
 #define LSG_JT_OCC 3
@@ -97,6 +97,7 @@ struct JoinParams {
   unsigned long long *inc_keys;
   size_t n_incidents;
   lsg_feature *feat;             // optional: count / sum / log2 sketch per (incident, signal) next to the maxima
+  uint32_t seg_max;              // k_join_ring: spans per segment at most
 };
 
 // one span's enriched value of one signal into the incident's features (the same bins as k_incident_accumulate)
@@ -482,7 +483,7 @@ __device__ __forceinline__ SpanRec span_from_halves(const uint4 sa, const uint4 
 // does not fit a tile) is left to k_join_big.
 constexpr int TM_CAP = LSG_TM_CAP;    // events per tile (28 B each; three CTAs per SM)
 #ifndef LSG_TM_LIST
-#define LSG_TM_LIST 32
+#define LSG_TM_LIST 48
 #endif
 constexpr int TM_LIST = LSG_TM_LIST;     // noted candidates per span
 constexpr int TM_MAX_F = 8;      // largest fanout the tile kernel keeps in registers
@@ -1066,6 +1067,8 @@ int lsg_launch_join(lsg_ctx *ctx, const JoinArgs &a) {
   p.counters = (unsigned long long *)a.counters;
   p.inc_keys = a.inc_keys; p.n_incidents = a.n_incidents;
   p.feat = a.feat;
+  static const int seg_env = getenv("LSG_RING_SEG") ? atoi(getenv("LSG_RING_SEG")) : 0;
+  p.seg_max = seg_env > 0 ? (uint32_t)seg_env : RG_SEG_MAX;
   const size_t n_chunks = (a.n_spans + JT_CH - 1) / JT_CH;
   const size_t smem = sizeof(TileSmem);
   // spans that do not fit a tile are listed for k_join_big; the list lives behind the ranges

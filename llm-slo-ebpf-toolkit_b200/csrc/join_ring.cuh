@@ -70,7 +70,8 @@ k_join_ring(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_lis
       const unsigned long long cur = *reinterpret_cast<volatile unsigned long long *>(seg_cursor);
       const unsigned long long rem = cur < n_sp ? n_sp - cur : 0;
       unsigned long long take = rem / (2ull * gridDim.x);
-      take = take < (unsigned long long)JT_CH ? (unsigned long long)JT_CH : (take > RG_SEG_MAX ? RG_SEG_MAX : take);
+      take = take > p.seg_max ? p.seg_max : take;
+      take = take < (unsigned long long)JT_CH ? (unsigned long long)JT_CH : take;
       const unsigned long long start = atomicAdd(seg_cursor, take);
       sm.seg_lo = (uint32_t)(start < n_sp ? start : n_sp);
       sm.seg_hi = (uint32_t)(start + take < n_sp ? start + take : n_sp);

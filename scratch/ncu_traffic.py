@@ -1,6 +1,6 @@
 """ncu --page raw --csv of a `--set full` capture -> per-kernel DRAM bytes per launch and a few utilisation figures
 (profiles/r01_ncu_traffic_<workload>.json, read by bench.py for roofline.traffic).
-usage: ncu_traffic.py raw.csv workload "source note" > out.json"""
+usage: ncu_traffic.py raw.csv workload "source note" [commit] > out.json"""
 import csv, json, re, sys
 rows = list(csv.reader(open(sys.argv[1])))
 hdr, units = rows[0], rows[1]
@@ -30,6 +30,8 @@ for r in rows[2:]:
     a['regs'] = int(f(r, 'launch__registers_per_thread') or 0)
     a['grid'] = int(f(r, 'launch__grid_size') or 0)
 out = {'source': sys.argv[3], 'workload': sys.argv[2], 'kernels': {}}
+if len(sys.argv) > 4:
+    out['commit'] = sys.argv[4]
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1]['us']):
     n = a['n']
     out['kernels'][k] = {'launches_captured': n, 'dram_bytes_per_launch': (a['rd'] + a['wr']) / n, 'dram_read': a['rd'] / n,
