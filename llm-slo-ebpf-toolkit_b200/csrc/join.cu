@@ -38,6 +38,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -490,6 +491,75 @@ constexpr int TM_MAX_F = 8;      // largest fanout the tile kernel keeps in regi
 constexpr int TM_HASH = JT_THREADS;    // hash slots for the chunk's span trace ids (<= 128 keys)
 constexpr uint16_t TM_END = 0xffffu;
 
+// ---- tiers 2-4 for one thread's share of a span's inner range (both forms of the tile kernel) -------------------
+// The events are the tile's shared-memory columns; `slot(g)` turns the loop variable into a column index (identity for
+// the fixed tile, `g mod capacity` for the ring).  The decision per event is predicate arithmetic on five loaded words.
+// A match at or above the threshold is not noted inside the loop (a divergent branch with a shared-memory atomic that
+// some lane of the warp takes in nearly every iteration): the loop runs in blocks of 32 events and collects the matches
+// of a block as bit masks, which are noted afterwards, every lane at its own pace.  With T32 the time deltas and the
+// tier limits are 32-bit (|dt| < 2^31 ns inside an inner range).
+struct PairSpan {
+  int64_t ts;
+  uint32_t s_lo, pod, cls, pid, conn, no_trace;
+  bool pod_ok, pid_ok, conn_ok, full;
+};
+struct TileCols {
+  const int64_t *ts;
+  const uint32_t *pod, *cls, *pid, *conn, *trsig;
+};
+
+template <bool T32, bool WITH4, int LIST, typename Slot>
+__device__ __forceinline__ void pair_scan(const TileCols c, const uint32_t beg, const uint32_t end, const Slot slot, const PairSpan &sp,
+                                          const uint64_t Wi, const int cut, uint32_t *n_note_k, uint16_t *note_k /* stride JT_CH */,
+                                          unsigned &n_match, unsigned &n_low, unsigned &n_unlisted) {
+  using dt_t = typename std::conditional<T32, uint32_t, uint64_t>::type;
+  const dt_t wi = (dt_t)Wi, w100 = (dt_t)(100 * kMs), w250 = (dt_t)(250 * kMs);
+  const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(c.ts);   // little endian: low words at even indices
+  for (uint32_t b = beg; b < end; b += 32) {
+    const uint32_t be = min(b + 32u, end);
+    uint32_t keep = 0, is2 = 0, is3 = 0;   // bit j: event b + j is a candidate to note / of tier 2 / of tier 3
+    uint32_t bit = 1u;
+    for (uint32_t g = b; g < be; ++g, bit <<= 1) {
+      const uint32_t sl = slot(g);
+      const uint32_t e_trsig = c.trsig[sl], e_pod = c.pod[sl], e_pid = c.pid[sl], e_conn = c.conn[sl];
+      dt_t ad;
+      if (T32) {
+        const int32_t d = (int32_t)(ts_lo[2 * sl] - sp.s_lo);
+        ad = (dt_t)(uint32_t)(d < 0 ? -d : d);
+      } else {
+        ad = (dt_t)lsg_absdiff(sp.ts, c.ts[sl]);
+      }
+      const bool in = ad <= wi, in100 = ad <= w100, in250 = ad <= w250;
+      const bool same_pod = sp.pod_ok & (e_pod == sp.pod);
+      const bool t2 = same_pod & sp.pid_ok & (e_pid == sp.pid) & in100;        // dns.go:61-64
+      const bool t3 = same_pod & sp.conn_ok & (e_conn == sp.conn) & in250;     // dns.go:65-68
+      bool t4 = false;
+      if (WITH4) t4 = c.cls[sl] == sp.cls;                                      // dns.go:69-73
+      const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : LSG_TIER_SVC_NODE;
+      // inside min(W, 500 ms), not a trace-id match (those belong to the hash pass), and some tier applies
+      const bool m = in & ((e_trsig >> 4) != sp.no_trace) & (t2 | t3 | t4);
+      n_match += m;
+      const bool low = m & (tier > cut);                                       // correlator.go:83-86
+      n_low += low;
+      const bool k = m & !low;
+      keep |= k ? bit : 0u;
+      is2 |= t2 ? bit : 0u;
+      is3 |= t3 ? bit : 0u;
+    }
+    if (sp.full) {
+      n_unlisted += __popc(keep);
+    } else {
+      while (keep) {
+        const int j = __ffs(keep) - 1;
+        keep &= keep - 1;
+        const int tier = (is2 >> j) & 1u ? LSG_TIER_POD_PID : (is3 >> j) & 1u ? LSG_TIER_POD_CONN : LSG_TIER_SVC_NODE;
+        const uint32_t at = atomicAdd(n_note_k, 1u);
+        if (at < (uint32_t)LIST) note_k[at * JT_CH] = (uint16_t)((tier << 12) | slot(b + j));
+      }
+    }
+  }
+}
+
 template <int F>
 struct TopF {
   uint64_t k1[F];   // (tier << 56) | |dt|
@@ -653,7 +723,11 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           for (int u = 0; u < LSG_JT_DEPTH; ++u) {
             r[u].a = make_uint4(0, 0, 0, 0);
             r[u].b = make_uint4(0xffffffffu, 0, 0, 0);   // padding: an identity row no table has
+#ifdef LSG_DEBUG_FAKE_GATHER   // timing experiment only (wrong results): every record comes from the same 32 KB, i.e. from L1
+            if (ub + u < PER && src[ub + u] != 0xffffffffu) r[u] = ld_nc_v8(p.events_in + (src[ub + u] & 1023u));
+#else
             if (ub + u < PER && src[ub + u] != 0xffffffffu) r[u] = ld_nc_v8(p.events_in + src[ub + u]);
+#endif
           }
 #pragma unroll
           for (int u = 0; u < LSG_JT_DEPTH; ++u) {
@@ -724,25 +798,12 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
           const uint32_t s_pod = spc.x, s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
           const bool pid_ok = s.pid != 0, conn_ok = s.conn != 0;
           const uint32_t zo = rg.z - A, wo = rg.w - A;
-          const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
-          const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);   // little endian: low words at even indices
-          const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;       // event trace ids are < 2^28
-          // |event time - span time|; when T32, |dt| < 2^31 ns for every event of an inner range and 32 bits are exact
-          auto absdt = [&](uint32_t o) -> uint64_t {
-            if (T32) {
-              const int32_t d = (int32_t)(ts_lo[2 * o] - s_lo);
-              return (uint64_t)(uint32_t)(d < 0 ? -d : d);
-            }
-            return lsg_absdiff(s.ts, sm.ts[o]);
-          };
-          auto note = [&](int tier, uint32_t o) {
-            if (full) {
-              n_unlisted++;
-            } else {
-              const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-              if (at < TM_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | o);
-            }
-          };
+          PairSpan ps;
+          ps.ts = s.ts; ps.s_lo = (uint32_t)(uint64_t)s.ts; ps.pod = spc.x; ps.cls = s_cls; ps.pid = s.pid; ps.conn = s.conn;
+          ps.no_trace = s.trace != 0 ? s.trace : 0xffffffffu;   // event trace ids are < 2^28
+          ps.pod_ok = pod_ok; ps.pid_ok = pid_ok; ps.conn_ok = conn_ok; ps.full = full;
+          const TileCols cols{sm.ts, sm.pod, sm.cls, sm.pid, sm.conn, sm.trsig};
+          const auto ident = [](uint32_t o) { return o; };
           if (cut < 4 && uniform) {
             // Every event this chunk can reach carries the same (service, node) class, and a service+node match is
             // below the threshold: it is only counted (correlator.go:83-86).  So count instead of enumerating:
@@ -753,50 +814,29 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
             const uint32_t x1 = r2.x - A, y1 = r2.y - A, z2 = r2.z - A, w2 = r2.w - A;
             uint32_t n_in = h ? 0u : y1 - x1;
             const uint32_t eb = h ? y1 : zo, ee = h ? wo : x1;      // lane 0: left edge, lane 1: right edge
-            for (uint32_t o = eb; o < ee; ++o) n_in += absdt(o) <= Wi;
-            const uint32_t m2 = z2 + ((w2 - z2) >> 1);
-            const uint32_t fb = h ? m2 : z2, fe = h ? w2 : m2;
-            uint32_t n23 = 0;
-            for (uint32_t o = fb; o < fe; ++o) {
-              const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
-              const uint64_t ad = absdt(o);
-              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
-              const bool same_pod = pod_ok & (e_pod == s_pod);
-              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
-              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
-              const int tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
-              const bool m = in & ((e_trsig >> 4) != no_trace) & (t2 | t3);
-              n23 += m;
-              n_match += m;
-              const bool low = m & (tier > cut);                                   // correlator.go:83-86
-              n_low += low;
-              if (m & !low) note(tier, o);
+            const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);
+            for (uint32_t o = eb; o < ee; ++o) {
+              if (T32) {
+                const int32_t d = (int32_t)(ts_lo[2 * o] - ps.s_lo);
+                n_in += (uint32_t)(d < 0 ? -d : d) <= (uint32_t)Wi;
+              } else {
+                n_in += lsg_absdiff(s.ts, sm.ts[o]) <= Wi;
+              }
             }
+            const uint32_t m2 = z2 + ((w2 - z2) >> 1);
+            const unsigned before = n_match;
+            pair_scan<T32, false, TM_LIST>(cols, h ? m2 : z2, h ? w2 : m2, ident, ps, Wi, cut, &sm.n_note[k], &sm.note[0][k], n_match,
+                                           n_low, n_unlisted);
             if (s_cls == sm.cls_min) {   // the span belongs to the tile's class: what is left inside the window is tier 4
-              uint32_t n4 = n_in - n23;                                            // may wrap per lane; the two-lane sum does not
+              uint32_t n4 = n_in - (n_match - before);                             // may wrap per lane; the two-lane sum does not
               if (!h) n4 -= sm.n_tr_in[k];
               n_match += n4;
               n_low += n4;
             }
           } else {
             const uint32_t mid = zo + ((wo - zo) >> 1);
-            const uint32_t beg = h ? mid : zo, end = h ? wo : mid;
-            for (uint32_t o = beg; o < end; ++o) {
-              // every operand is loaded up front (independent shared-memory loads), the decision is predicate arithmetic
-              const uint32_t e_trsig = sm.trsig[o], e_pod = sm.pod[o], e_cls = sm.cls[o], e_pid = sm.pid[o], e_conn = sm.conn[o];
-              const uint64_t ad = absdt(o);
-              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
-              const bool same_pod = pod_ok & (e_pod == s_pod), same_sn = e_cls == s_cls;
-              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
-              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
-              const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
-              // inside min(W, 500 ms), not a trace-id match (those belong to the hash pass), and some tier applies
-              const bool m = in & ((e_trsig >> 4) != no_trace) & (tier != 0);
-              n_match += m;
-              const bool low = m & (tier > cut);                                   // correlator.go:83-86
-              n_low += low;
-              if (m & !low) note(tier, o);
-            }
+            pair_scan<T32, true, TM_LIST>(cols, h ? mid : zo, h ? wo : mid, ident, ps, Wi, cut, &sm.n_note[k], &sm.note[0][k], n_match,
+                                          n_low, n_unlisted);
           }
         }
       }

@@ -224,74 +224,41 @@ k_join_ring(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_lis
           const bool pod_ok = spc.x != 0;
           const uint32_t s_pod = spc.x, s_cls = spc.y != 0 ? spc.y : 0xffffffffu;
           const bool pid_ok = s.pid != 0, conn_ok = s.conn != 0;
-          const uint32_t s_lo = (uint32_t)(uint64_t)s.ts;
-          const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);   // little endian: low words at even indices
-          const uint32_t no_trace = s.trace != 0 ? s.trace : 0xffffffffu;       // event trace ids are < 2^28
-          // |event time - span time| of the event in slot sl; when T32, |dt| < 2^31 ns inside an inner range
-          auto absdt = [&](uint32_t sl) -> uint64_t {
-            if (T32) {
-              const int32_t d = (int32_t)(ts_lo[2 * sl] - s_lo);
-              return (uint64_t)(uint32_t)(d < 0 ? -d : d);
-            }
-            return lsg_absdiff(s.ts, sm.ts[sl]);
-          };
-          auto note = [&](int tier, uint32_t sl) {
-            if (full) {
-              n_unlisted++;
-            } else {
-              const uint32_t at = atomicAdd(&sm.n_note[k], 1u);
-              if (at < RG_LIST) sm.note[at][k] = (uint16_t)((tier << 12) | sl);
-            }
-          };
+          PairSpan ps;
+          ps.ts = s.ts; ps.s_lo = (uint32_t)(uint64_t)s.ts; ps.pod = spc.x; ps.cls = s_cls; ps.pid = s.pid; ps.conn = s.conn;
+          ps.no_trace = s.trace != 0 ? s.trace : 0xffffffffu;   // event trace ids are < 2^28
+          ps.pod_ok = pod_ok; ps.pid_ok = pid_ok; ps.conn_ok = conn_ok; ps.full = full;
+          const TileCols cols{sm.ts, sm.pod, sm.cls, sm.pid, sm.conn, sm.trsig};
+          const auto ring = [](uint32_t g) { return g & RG_MASK; };
           if (cut < 4 && uniform) {
             // one (service, node) class in the whole tile and a service+node match is below the threshold: tier 4 is
             // counted (events inside the inner window - trace-id matches among them - tier 2/3 matches), see k_join_tiles
             uint32_t n_in = h ? 0u : r2.y - r2.x;
             const uint32_t eb = h ? r2.y : rg.z, ee = h ? rg.w : r2.x;      // lane 0: left edge, lane 1: right edge
-            for (uint32_t g = eb; g < ee; ++g) n_in += absdt(g & RG_MASK) <= Wi;
-            const uint32_t m2 = r2.z + ((r2.w - r2.z) >> 1);
-            const uint32_t fb = h ? m2 : r2.z, fe = h ? r2.w : m2;
-            uint32_t n23 = 0;
-            for (uint32_t g = fb; g < fe; ++g) {
+            const uint32_t *ts_lo = reinterpret_cast<const uint32_t *>(sm.ts);
+            for (uint32_t g = eb; g < ee; ++g) {
               const uint32_t sl = g & RG_MASK;
-              const uint32_t e_trsig = sm.trsig[sl], e_pod = sm.pod[sl], e_pid = sm.pid[sl], e_conn = sm.conn[sl];
-              const uint64_t ad = absdt(sl);
-              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
-              const bool same_pod = pod_ok & (e_pod == s_pod);
-              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
-              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
-              const int tier = t2 ? LSG_TIER_POD_PID : LSG_TIER_POD_CONN;
-              const bool m = in & ((e_trsig >> 4) != no_trace) & (t2 | t3);
-              n23 += m;
-              n_match += m;
-              const bool low = m & (tier > cut);                                   // correlator.go:83-86
-              n_low += low;
-              if (m & !low) note(tier, sl);
+              if (T32) {
+                const int32_t d = (int32_t)(ts_lo[2 * sl] - ps.s_lo);
+                n_in += (uint32_t)(d < 0 ? -d : d) <= (uint32_t)Wi;
+              } else {
+                n_in += lsg_absdiff(s.ts, sm.ts[sl]) <= Wi;
+              }
             }
+            const uint32_t m2 = r2.z + ((r2.w - r2.z) >> 1);
+            const unsigned before = n_match;
+            pair_scan<T32, false, RG_LIST>(cols, h ? m2 : r2.z, h ? r2.w : m2, ring, ps, Wi, cut, &sm.n_note[k], &sm.note[0][k], n_match,
+                                           n_low, n_unlisted);
             if (s_cls == sm.cls_min) {   // the span belongs to the tile's class: what is left inside the window is tier 4
-              uint32_t n4 = n_in - n23;                                            // may wrap per lane; the two-lane sum does not
+              uint32_t n4 = n_in - (n_match - before);                             // may wrap per lane; the two-lane sum does not
               if (!h) n4 -= sm.n_tr_in[k];
               n_match += n4;
               n_low += n4;
             }
           } else {
             const uint32_t mid = rg.z + ((rg.w - rg.z) >> 1);
-            const uint32_t beg = h ? mid : rg.z, end = h ? rg.w : mid;
-            for (uint32_t g = beg; g < end; ++g) {
-              const uint32_t sl = g & RG_MASK;
-              const uint32_t e_trsig = sm.trsig[sl], e_pod = sm.pod[sl], e_cls = sm.cls[sl], e_pid = sm.pid[sl], e_conn = sm.conn[sl];
-              const uint64_t ad = absdt(sl);
-              const bool in = ad <= Wi, in100 = ad <= (uint64_t)(100 * kMs), in250 = ad <= (uint64_t)(250 * kMs);
-              const bool same_pod = pod_ok & (e_pod == s_pod), same_sn = e_cls == s_cls;
-              const bool t2 = same_pod & pid_ok & (e_pid == s.pid) & in100;        // dns.go:61-64
-              const bool t3 = same_pod & conn_ok & (e_conn == s.conn) & in250;     // dns.go:65-68
-              const int tier = t2 ? LSG_TIER_POD_PID : t3 ? LSG_TIER_POD_CONN : same_sn ? LSG_TIER_SVC_NODE : 0;   // dns.go:69-73
-              const bool m = in & ((e_trsig >> 4) != no_trace) & (tier != 0);
-              n_match += m;
-              const bool low = m & (tier > cut);                                   // correlator.go:83-86
-              n_low += low;
-              if (m & !low) note(tier, sl);
-            }
+            pair_scan<T32, true, RG_LIST>(cols, h ? mid : rg.z, h ? rg.w : mid, ring, ps, Wi, cut, &sm.n_note[k], &sm.note[0][k], n_match,
+                                          n_low, n_unlisted);
           }
         }
       }
