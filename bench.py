@@ -116,6 +116,17 @@ class ClockSampler:
         return out
 
 
+_T0 = time.perf_counter()
+
+
+def progress(env, msg):
+    """One line on stderr per stage (rank 0, or every rank with LSG_BENCH_TRACE=1): where a run that never prints its JSON
+    line stopped."""
+    if env.get("rank", 0) == 0 or os.environ.get("LSG_BENCH_TRACE"):
+        sys.stderr.write("[bench %7.1fs rank %d] %s\n" % (time.perf_counter() - _T0, env.get("rank", 0), msg))
+        sys.stderr.flush()
+
+
 def workload_cfg(name, rank, world):
     from llm_slo_ebpf_toolkit_b200 import synth
     if name == "c2":
@@ -331,6 +342,7 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
             dist.barrier()
 
     with torch.cuda.stream(stream):
+        progress(env, "%s: generating the shard on the device" % name)
         wl = DeviceWorkload(ctx, cfg)
         if key_hint:
             wl.state_key_range()   # a replay knows its window: no readback of the key layout inside the step
@@ -359,10 +371,12 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
                     pending[b].wait()
                     pending[b] = None
 
+        progress(env, "%s: warm-up" % name)
         for _ in range(warmup):
             step()
         drain()
         barrier()
+        progress(env, "%s: %d timed steps" % (name, steps))
         sort_info = ctx.last_sort_info()
         launches0 = ctx.launch_count()
         if env.get("sampler"):
@@ -380,6 +394,7 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
         # per-kernel durations: the same steps again with a CUDA-event pair around every kernel.  The pairs cost a few
         # percent of the step, so they are kept out of the region `value` is taken from.
         prof_steps = min(steps, prof_steps_max)
+        progress(env, "%s: %.3f ms/step on this rank; per-kernel pass" % (name, ms / steps))
         ctx.profile_read(reset=True)
         ctx.profile_enable(True)
         evp0, evp1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -397,11 +412,13 @@ def device_leg(env, name, steps, warmup, key_hint=True, prof_steps_max=50, keep=
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_max = float(t.item())
         # ---- checks: one more batch without the reduction gives this rank's own counters
+        progress(env, "%s: checks (counter invariants, sampled groups on the CPU oracle)" % name)
         b = step(reduce=False)
         barrier()
         wl.counters = blocks[b]
         local = wl.read_counters()
         ok, det = verify_batch(torch, wl, local, A)
+        progress(env, "%s: checks done on this rank: %s" % (name, ok))
         if world > 1:
             # the allreduced block of the timed region must be the sum of the ranks' own blocks (same inputs every step)
             gathered = [torch.zeros_like(blocks[b]) for _ in range(world)]
@@ -724,7 +741,9 @@ def main():
     main_res, wl = device_leg(env, args.workload, args.steps, args.warmup, key_hint=not args.no_key_hint, keep=True)
     clocks = sampler.stop()
     env["sampler"] = None
+    progress(env, "device-resident leg done; end-to-end leg" if not args.no_e2e else "device-resident leg done")
     e2e = None if args.no_e2e else measure_e2e(env, wl, args)
+    progress(env, "end-to-end leg done")
     n_events_main = wl.n_events
     del wl
     torch.cuda.empty_cache()
@@ -767,10 +786,12 @@ def main():
         except Exception as e:   # the headline line must survive a failure of an extra leg
             configs["c3"] = {"error": "%s: %s" % (type(e).__name__, e)}
         try:
+            progress(env, "attribution-only leg")
             configs["attribution_only"] = attribution_leg(env, 40_000_000 // 8 if world > 1 else 40_000_000)
         except Exception as e:
             configs["attribution_only"] = {"error": "%s: %s" % (type(e).__name__, e)}
 
+    progress(env, "all legs done")
     if rank == 0:
         r = main_res
         line = {

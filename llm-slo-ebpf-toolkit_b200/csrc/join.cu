@@ -235,6 +235,9 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// generic-proxy accesses of a shared-memory buffer (the previous tile's reads) ordered before an async-proxy write to it
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 constexpr int JT_LIST = 64;    // per-warp candidate list (entries); compacted to the best `fanout` when it fills
 
 struct Cand {
@@ -590,7 +593,7 @@ struct TileSmem {
   uint32_t conn[TM_CAP];
   uint32_t trsig[TM_CAP];
   uint4 span[JT_CH][2];
-  uint4 rng[JT_CH];
+  uint4 rngbuf[2][JT_CH];           // this chunk's ranges and, arriving by bulk copy meanwhile, the next chunk's
   uint4 rng2[JT_CH];
   uint32_t sidx[JT_CH];
   uint16_t note[TM_LIST][JT_CH];    // entry-major: consecutive spans, consecutive halfwords
@@ -603,6 +606,7 @@ struct TileSmem {
   uint16_t hnext[JT_CH];            // next span with the same trace id
   unsigned long long cnt[5];
   uint64_t bar;
+  uint64_t bar_rng;
 };
 
 __device__ __forceinline__ uint32_t trace_slot(uint32_t tr) { return (tr * 2654435761u) >> (TM_HASH == 256 ? 24 : TM_HASH == 128 ? 25 : 23); }
@@ -617,11 +621,22 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
   const unsigned tid = threadIdx.x, lane = tid & 31;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
   if (tid < 5) sm.cnt[tid] = 0;
-  if (tid == 0) mbar_init(&sm.bar, 1);
+  if (tid == 0) { mbar_init(&sm.bar, 1); mbar_init(&sm.bar_rng, 1); }
   __syncthreads();
-  uint32_t phase = 0;
+  uint32_t phase = 0, rphase = 0;
+  int cur = 0;
   unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
   const size_t n_chunks = (p.n_spans + JT_CH - 1) / JT_CH;
+  // The chunk's ranges (16 B per span, contiguous) come by TMA bulk copy, one chunk ahead: thread 0 asks for the next
+  // chunk's while this one is worked on, so the tile bounds never wait for a global load.
+  auto fetch_ranges = [&](const size_t c, const int buf) {
+    const size_t q = c * JT_CH;
+    const uint32_t bytes = (uint32_t)min((size_t)JT_CH, p.n_spans - q) * (uint32_t)sizeof(uint4);
+    fence_proxy_async();
+    mbar_expect_tx(&sm.bar_rng, bytes);
+    bulk_g2s(sm.rngbuf[buf], p.ranges + q, bytes, &sm.bar_rng);
+  };
+  if (tid == 0 && blockIdx.x < n_chunks) fetch_ranges(blockIdx.x, 0);
   const uint64_t W = (uint64_t)p.window_ns;
   const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
   // confidence falls with the tier (1.0, 0.9, 0.8, 0.65), so "confidence >= threshold" is "tier <= cut"
@@ -631,8 +646,8 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     const size_t q0 = chunk * JT_CH;
     const int nq = (int)min((size_t)JT_CH, p.n_spans - q0);
     // ---- stage the chunk's spans: input index, ranges, record (two 16-byte halves per span); clear the hash
+    const uint4 *rng = sm.rngbuf[cur];
     if ((int)tid < nq) {
-      sm.rng[tid] = p.ranges[q0 + tid];
       sm.rng2[tid] = p.ranges2[q0 + tid];
       sm.sidx[tid] = p.span_perm ? p.span_perm[q0 + tid] : (uint32_t)(q0 + tid);
     }
@@ -643,7 +658,14 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     }
     sm.hkey[tid] = 0;            // JT_THREADS == TM_HASH
     sm.hhead[tid] = TM_END;
+    mbar_wait(&sm.bar_rng, rphase);   // this chunk's ranges have landed (asked for one chunk ago)
+    rphase ^= 1;
     __syncthreads();
+    // Only now, when every thread has seen this phase complete, may the barrier be armed again (a thread still polling
+    // while two phases complete would wait for a third).  The other buffer held the previous chunk's ranges, which
+    // nobody reads past that chunk's last barrier.
+    if (tid == 0 && chunk + gridDim.x < n_chunks) fetch_ranges(chunk + gridDim.x, cur ^ 1);
+    cur ^= 1;
     // ---- hash of the chunk's non-zero span trace ids; spans that share an id are chained
     if ((int)tid < nq) {
       const uint32_t tr = sm.span[tid][1].y;
@@ -666,11 +688,11 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
     }
     int i0 = 0;
     while (i0 < nq) {
-      const uint32_t A = sm.rng[i0].x & ~3u;   // 16-byte aligned start for every column
+      const uint32_t A = rng[i0].x & ~3u;   // 16-byte aligned start for every column
       if (tid == 0) { sm.cls_min = 0xffffffffu; sm.cls_max = 0u; }   // published by the barrier below
       if (FUSED && (int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }   // the loader already notes
       // spans of the chunk whose outer range still ends inside a tile that starts at A (ranges are monotone)
-      const bool fits = (int)tid >= i0 && (int)tid < nq && sm.rng[tid].y - A <= (uint32_t)(TM_CAP - 4);
+      const bool fits = (int)tid >= i0 && (int)tid < nq && rng[tid].y - A <= (uint32_t)(TM_CAP - 4);
       const int n_fit = __syncthreads_count(fits);
       if (n_fit == 0) {
         // this span's own range is larger than a tile: leave it to k_join_big
@@ -679,10 +701,10 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         continue;
       }
       const int i1 = i0 + n_fit;
-      const uint32_t Bend = (sm.rng[i1 - 1].y + 3u) & ~3u;
+      const uint32_t Bend = (rng[i1 - 1].y + 3u) & ~3u;
       const uint32_t count = Bend > A ? Bend - A : 0;   // <= TM_CAP, multiple of 4; the columns are padded past n
       if (!FUSED && (int)tid < JT_CH) { sm.n_note[tid] = 0; sm.n_tr[tid] = 0; sm.n_tr_in[tid] = 0; }
-      const uint32_t live_beg = sm.rng[i0].x - A, live_end = min(count, sm.rng[i1 - 1].y - A);
+      const uint32_t live_beg = rng[i0].x - A, live_end = min(count, rng[i1 - 1].y - A);
       uint32_t cmin = 0xffffffffu, cmax = 0u;
       // tier 1 for one tile event: probe the hash of the chunk's span trace ids, note the spans it falls into
       auto probe_trace = [&](const uint32_t o, const uint32_t tr, const int64_t e_ts) {
@@ -693,7 +715,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         if (key != tr) return;
         for (uint32_t k = sm.hhead[slot]; k != TM_END; k = sm.hnext[k]) {
           if ((int)k < i0 || (int)k >= i1) continue;                 // that span belongs to another tile of the chunk
-          const uint4 rg = sm.rng[k];
+          const uint4 rg = rng[k];
           if (o + A < rg.x || o + A >= rg.y) continue;                // outside its range: cannot be within the window
           const int64_t s_ts = (int64_t)(((uint64_t)sm.span[k][0].y << 32) | sm.span[k][0].x);
           const uint64_t adt = lsg_absdiff(s_ts, e_ts);
@@ -748,6 +770,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         }
       } else if (count) {
         if (tid == 0) {
+          fence_proxy_async();
           mbar_expect_tx(&sm.bar, count * 24u);
           bulk_g2s(sm.ts, p.ev.ts + A, count * 8u, &sm.bar);
           bulk_g2s(sm.trsig, p.ev.trsig + A, count * 4u, &sm.bar);
@@ -788,7 +811,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       s.ts = 0; s.ident = 0; s.pid = 0; s.conn = 0; s.trace = 0; s.incident = LSG_NONE;
       if (live) {
         s = span_from_halves(sm.span[k][0], sm.span[k][1]);
-        const uint4 rg = sm.rng[k];
+        const uint4 rg = rng[k];
         // `fanout` trace-id matches (confidence 1.0) already noted: a tier 2-4 candidate can be counted but never kept
         const bool full = cut >= 1 && sm.n_tr[k] >= (uint32_t)p.fanout;
         if (rg.z < rg.w && rg.z != 0xffffffffu) {
@@ -848,7 +871,7 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
       bool redo = false;
       if (live) {
         n_cand = sm.n_note[k];
-        redo = n_cand > (uint32_t)TM_LIST || sm.rng[k].z == 0xffffffffu;
+        redo = n_cand > (uint32_t)TM_LIST || rng[k].z == 0xffffffffu;
         if (!redo) {
 #pragma unroll 2
           for (uint32_t i = h; i < n_cand; i += 2) {
