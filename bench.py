@@ -771,9 +771,59 @@ def main():
                                   "on %d events x %d spans at C2's density, %d passes; the literal brute force is timed by "
                                   "--impl reference" % (ne, ns, reps)}
 
+    # ---- the one JSON line: built now, so that it survives an extra leg that hangs ---------------------------
+    import threading
+    r = main_res
+    emit_lock = threading.Lock()
+    emitted = {"done": False}
+
+    def emit(configs):
+        """Rank 0 prints the line, once."""
+        with emit_lock:
+            if emitted["done"]:
+                return
+            emitted["done"] = True
+            if rank != 0:
+                return
+            line = {
+                "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int64 keys / f64 scores", "data": "synthetic",
+                "incidents_per_s": r["incidents_per_s"],
+                "config": {"workload": r["workload"], "events_per_gpu": r["events_per_gpu"], "spans_per_gpu": r["spans_per_gpu"],
+                           "incidents_per_gpu": r["incidents_per_gpu"], "window_ms": 2000, "threshold": 0.7, "fanout": 3,
+                           "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((r["events_per_gpu"] + r["spans_per_gpu"]) * 32 / 1e6),
+                           "sort": r["sort"],
+                           "key_hint": "spans' time range and group count stated by the caller (checked on the device; --no-key-hint reads the key layout back instead)" if not args.no_key_hint else "none",
+                           "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS),
+                           "numa": numa},
+                "e2e": e2e,
+                "gpu_launches": r["gpu_launches"],
+                "roofline": r["roofline"],
+                "pipeline_roofline": r["pipeline_roofline"],
+                "kernels": r["kernels"],
+                "kernel_timing": r["kernel_timing"],
+                "cpu_baseline": cpu_baseline,
+                "clocks": clocks,
+                "checks": r["checks"],
+                "configs": configs,
+            }
+            out.write(json.dumps(line) + "\n")
+            out.flush()
+
     # ---- the other configurations BASELINE.json names, in the same process -------------------------------
     configs = {}
     if not args.no_extra and args.workload == "c2":
+        budget = float(os.environ.get("LSG_BENCH_EXTRA_BUDGET_S", "600"))
+
+        def give_up():
+            progress(env, "the extra legs did not finish within %.0f s: printing the line without them" % budget)
+            emit(dict(configs, error="extra legs (C3 / attribution only) exceeded %.0f s and were abandoned" % budget))
+            os._exit(0)
+
+        watchdog = threading.Timer(budget, give_up)
+        watchdog.daemon = True
+        watchdog.start()
         try:
             free = torch.cuda.mem_get_info()[0]
             if free > 150 * (1 << 30):
@@ -790,35 +840,10 @@ def main():
             configs["attribution_only"] = attribution_leg(env, 40_000_000 // 8 if world > 1 else 40_000_000)
         except Exception as e:
             configs["attribution_only"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        watchdog.cancel()
 
     progress(env, "all legs done")
-    if rank == 0:
-        r = main_res
-        line = {
-            "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int64 keys / f64 scores", "data": "synthetic",
-            "incidents_per_s": r["incidents_per_s"],
-            "config": {"workload": r["workload"], "events_per_gpu": r["events_per_gpu"], "spans_per_gpu": r["spans_per_gpu"],
-                       "incidents_per_gpu": r["incidents_per_gpu"], "window_ms": 2000, "threshold": 0.7, "fanout": 3,
-                       "l2": "inputs larger than L2 (%.0f MB of records per step)" % ((r["events_per_gpu"] + r["spans_per_gpu"]) * 32 / 1e6),
-                       "sort": r["sort"],
-                       "key_hint": "spans' time range and group count stated by the caller (checked on the device; --no-key-hint reads the key layout back instead)" if not args.no_key_hint else "none",
-                       "parallelism": "shard by pod identity x%d, sum-allreduce of %d counters" % (world, A.COUNTER_WORDS),
-                       "numa": numa},
-            "e2e": e2e,
-            "gpu_launches": r["gpu_launches"],
-            "roofline": r["roofline"],
-            "pipeline_roofline": r["pipeline_roofline"],
-            "kernels": r["kernels"],
-            "kernel_timing": r["kernel_timing"],
-            "cpu_baseline": cpu_baseline,
-            "clocks": clocks,
-            "checks": r["checks"],
-            "configs": configs,
-        }
-        out.write(json.dumps(line) + "\n")
-        out.flush()
+    emit(configs)
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
