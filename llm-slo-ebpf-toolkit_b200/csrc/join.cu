@@ -585,6 +585,146 @@ struct TopF {
   }
 };
 
+// ---- what the tile kernels do with a span once its matches are noted ---------------------------------------------
+// Called by every thread of the warp (shuffles inside); lanes 2k and 2k + 1 serve one span, h = lane & 1.
+//   order  lane h takes the span's notes of parity h, then the odd lane hands its best F to the even lane: the
+//          reference's order (tier, |dt|, input index), correlator.go:92-99
+//   write  the even lane owns the span's candidates, confidence and counters (correlator.go:101-118); the twelve
+//          attribute columns are split between the two lanes (six each), which both read the kept candidates' values
+//          and signals; per-incident maxima (and optional features) by atomics: the A7 glue
+// `pos_of` turns a note's column index into the event's sorted position, `slot_of` a sorted position into its column
+// index.  A span whose list overflowed (or whose time was clamped into the key space) is listed for k_join_big.
+struct TileTotals {
+  unsigned long long matched = 0, low = 0, drop = 0, cand = 0, kept = 0;
+};
+
+template <int F, bool FUSED, int LIST, typename PosOf, typename SlotOf>
+__device__ __forceinline__ void span_epilogue(const JoinParams &p, const TileCols c, const uint16_t *note_k /* stride JT_CH */,
+                                              const uint32_t n_noted, const uint32_t n_tr, const bool live, const bool clamped,
+                                              const SpanRec &s, const size_t si, const uint32_t span_pos, const unsigned h,
+                                              const unsigned lane, const int cut, unsigned n_match, unsigned n_low, unsigned n_unlisted,
+                                              const PosOf pos_of, const SlotOf slot_of, uint32_t *big_list, unsigned int *big_count,
+                                              TileTotals &w) {
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  TopF<F> top;
+  top.init();
+  uint32_t n_cand = 0;
+  bool redo = false;
+  if (live) {
+    n_cand = n_noted;
+    redo = n_cand > (uint32_t)LIST || clamped;
+    if (!redo) {
+#pragma unroll 2
+      for (uint32_t i = h; i < n_cand; i += 2) {
+        const uint32_t e = note_k[i * JT_CH];
+        const uint32_t sl = e & 0xfffu, tier = e >> 12;
+        const uint32_t g = pos_of(sl);
+        const uint64_t adt = lsg_absdiff(s.ts, c.ts[sl]);
+        top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[g], g);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < F; ++r) {
+    const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
+    const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
+    const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
+    if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
+  }
+  n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
+  n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
+  n_unlisted += __shfl_down_sync(0xffffffffu, n_unlisted, 1);
+  n_cand += n_unlisted;   // candidates that were counted without being noted
+  if (!live) return;
+  if (redo) {
+    if (!h) big_list[atomicAdd(big_count, 1u)] = span_pos;   // more candidates than the list holds
+    return;
+  }
+  const unsigned pair = 3u << (lane & 30u);
+  double vals[F];
+  unsigned sigs[F];
+  unsigned present = 0;
+  int kept = 0;
+#pragma unroll
+  for (int r = 0; r < F; ++r) {
+    const bool mine = r < p.fanout && top.idx[r] != 0xffffffffu;
+    const uint32_t pos = __shfl_sync(pair, mine ? top.pos[r] : 0xffffffffu, lane & 30u);   // the even lane's final list
+    const bool has = pos != 0xffffffffu;
+    // the candidate's value: from the sorted column, or from its input record when there is no sorted copy
+    const uint32_t in_idx = __shfl_sync(pair, top.idx[r], lane & 30u);
+    vals[r] = !has ? 0.0 : FUSED ? p.events_in[in_idx].value : p.ev.val[pos];
+    sigs[r] = has ? (c.trsig[slot_of(pos)] & 15u) : 0xffu;
+    kept += has;
+    present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
+    if (!h && r < p.fanout) {
+      p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
+      p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
+      if (p.cand_value) p.cand_value[si * (size_t)p.fanout + r] = vals[r];
+      if (p.cand_sig) p.cand_sig[si * (size_t)p.fanout + r] = (uint8_t)sigs[r];
+    }
+  }
+  // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
+  double v0 = nan, v3 = nan, v4 = nan;
+  const bool to_incident = p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents;
+#pragma unroll
+  for (int cc = 0; cc < LSG_NSIG / 2; ++cc) {
+    const unsigned col = h * (LSG_NSIG / 2) + cc;
+    double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
+    if ((present >> col) & 1u) {
+#pragma unroll
+      for (int r = 0; r < F; ++r)
+        if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
+    }
+    if (p.attr_out) p.attr_out[si * LSG_NSIG + col] = v;
+    if (to_incident && !isnan(v)) {
+      atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
+      if (p.feat) feat_add(p.feat, (size_t)s.incident * LSG_NSIG + col, v);
+    }
+    if (cc == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
+    if (cc == 3) v3 = v;
+    if (cc == 4) v4 = v;
+  }
+  if (!h) {
+    n_match += n_tr;
+    if (cut < 1) n_low += n_tr;
+    // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
+    if (p.conf_out) p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
+    if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
+      double total = 0.0;
+      if (!isnan(v0)) total += v0;
+      if (!isnan(v3)) total += v3;
+      if (!isnan(v4)) total += v4;
+      p.retrieval_out[si] = total;
+    }
+    if (p.n_cand_out) p.n_cand_out[si] = n_cand;
+    w.matched += n_match;
+    w.low += n_low;
+    w.cand += n_cand;
+    w.kept += kept;
+    if (n_cand > (uint32_t)p.fanout) w.drop += n_cand - p.fanout;   // correlator.go:101-103
+  }
+}
+
+// block-level sum of the per-thread totals into the five join counters: lanes -> warp -> block -> one atomic each
+__device__ __forceinline__ void flush_totals(TileTotals w, unsigned long long *block_cnt /* shared, zeroed */, unsigned long long *counters) {
+  for (int o = 16; o; o >>= 1) {
+    w.matched += __shfl_xor_sync(0xffffffffu, w.matched, o);
+    w.low += __shfl_xor_sync(0xffffffffu, w.low, o);
+    w.drop += __shfl_xor_sync(0xffffffffu, w.drop, o);
+    w.cand += __shfl_xor_sync(0xffffffffu, w.cand, o);
+    w.kept += __shfl_xor_sync(0xffffffffu, w.kept, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (w.matched) atomicAdd(&block_cnt[0], w.matched);
+    if (w.low) atomicAdd(&block_cnt[1], w.low);
+    if (w.drop) atomicAdd(&block_cnt[2], w.drop);
+    if (w.cand) atomicAdd(&block_cnt[3], w.cand);
+    if (w.kept) atomicAdd(&block_cnt[4], w.kept);
+  }
+  __syncthreads();
+  if (threadIdx.x < 5 && block_cnt[threadIdx.x]) atomicAdd(&counters[threadIdx.x], block_cnt[threadIdx.x]);
+}
+
 struct TileSmem {
   int64_t ts[TM_CAP];
   uint32_t pod[TM_CAP];             // staged as the identity row, rewritten in place to the row's pod id
@@ -619,13 +759,12 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TileSmem &sm = *reinterpret_cast<TileSmem *>(smem_raw);
   const unsigned tid = threadIdx.x, lane = tid & 31;
-  const double nan = __longlong_as_double(0x7ff8000000000000ll);
   if (tid < 5) sm.cnt[tid] = 0;
   if (tid == 0) { mbar_init(&sm.bar, 1); mbar_init(&sm.bar_rng, 1); }
   __syncthreads();
   uint32_t phase = 0, rphase = 0;
   int cur = 0;
-  unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
+  TileTotals w;
   const size_t n_chunks = (p.n_spans + JT_CH - 1) / JT_CH;
   // The chunk's ranges (16 B per span, contiguous) come by TMA bulk copy, one chunk ahead: thread 0 asks for the next
   // chunk's while this one is worked on, so the tile bounds never wait for a global load.
@@ -864,130 +1003,20 @@ k_join_tiles(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_li
         }
       }
       __syncwarp();      // the two lanes of a span sit in one warp: their notes are visible to each other now
-      // ---- order: lane h takes the notes of parity h, then the odd lane hands its best F to the even lane
-      TopF<F> top;
-      top.init();
-      uint32_t n_cand = 0;
-      bool redo = false;
-      if (live) {
-        n_cand = sm.n_note[k];
-        redo = n_cand > (uint32_t)TM_LIST || rng[k].z == 0xffffffffu;
-        if (!redo) {
-#pragma unroll 2
-          for (uint32_t i = h; i < n_cand; i += 2) {
-            const uint32_t e = sm.note[i][k];
-            const uint32_t o = e & 0xfffu, tier = e >> 12;
-            const uint64_t adt = lsg_absdiff(s.ts, sm.ts[o]);
-            top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[A + o], A + o);
-          }
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < F; ++r) {
-        const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
-        const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
-        const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
-        if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
-      }
-      n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
-      n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
-      n_unlisted += __shfl_down_sync(0xffffffffu, n_unlisted, 1);
-      n_cand += n_unlisted;   // candidates that were counted without being noted
-      // ---- write: the even lane owns the span's candidates, confidence and counters; the twelve attribute columns
-      //      are split between the two lanes (six each), which both read the kept candidates' values and signals
-      if (live) {
-        if (redo) {
-          if (!h) big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q0 + k);   // more candidates than the list holds
-        } else {
-          const unsigned pair = 3u << (lane & 30u);
-          const size_t si = sm.sidx[k];
-          double vals[F];
-          unsigned sigs[F];
-          unsigned present = 0;
-          int kept = 0;
-#pragma unroll
-          for (int r = 0; r < F; ++r) {
-            const bool mine = r < p.fanout && top.idx[r] != 0xffffffffu;
-            const uint32_t pos = __shfl_sync(pair, mine ? top.pos[r] : 0xffffffffu, lane & 30u);   // the even lane's final list
-            const bool has = pos != 0xffffffffu;
-            // the candidate's value: from the sorted column, or from its input record when there is no sorted copy
-            const uint32_t in_idx = __shfl_sync(pair, top.idx[r], lane & 30u);
-            vals[r] = !has ? 0.0 : FUSED ? p.events_in[in_idx].value : p.ev.val[pos];
-            sigs[r] = has ? (sm.trsig[pos - A] & 15u) : 0xffu;
-            kept += has;
-            present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
-            if (!h && r < p.fanout) {
-              p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
-              p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
-              if (p.cand_value) p.cand_value[si * (size_t)p.fanout + r] = vals[r];
-              if (p.cand_sig) p.cand_sig[si * (size_t)p.fanout + r] = (uint8_t)sigs[r];
-            }
-          }
-          // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
-          double v0 = nan, v3 = nan, v4 = nan;
-          const bool to_incident = p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents;
-#pragma unroll
-          for (int c = 0; c < LSG_NSIG / 2; ++c) {
-            const unsigned col = h * (LSG_NSIG / 2) + c;
-            double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
-            if ((present >> col) & 1u) {
-#pragma unroll
-              for (int r = 0; r < F; ++r)
-                if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
-            }
-            if (p.attr_out) p.attr_out[si * LSG_NSIG + col] = v;
-            if (to_incident && !isnan(v)) {
-              atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
-              if (p.feat) feat_add(p.feat, (size_t)s.incident * LSG_NSIG + col, v);
-            }
-            if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
-            if (c == 3) v3 = v;
-            if (c == 4) v4 = v;
-          }
-          if (!h) {
-            const uint32_t n_tr = sm.n_tr[k];
-            n_match += n_tr;
-            if (cut < 1) n_low += n_tr;
-            // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
-            if (p.conf_out) p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
-            if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
-              double total = 0.0;
-              if (!isnan(v0)) total += v0;
-              if (!isnan(v3)) total += v3;
-              if (!isnan(v4)) total += v4;
-              p.retrieval_out[si] = total;
-            }
-            if (p.n_cand_out) p.n_cand_out[si] = n_cand;
-            w_matched += n_match;
-            w_low += n_low;
-            w_cand += n_cand;
-            w_kept += kept;
-            if (n_cand > (uint32_t)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
-          }
-        }
+      // ---- order the span's notes, write its outputs (span_epilogue)
+      {
+        const TileCols cols{sm.ts, sm.pod, sm.cls, sm.pid, sm.conn, sm.trsig};
+        span_epilogue<F, FUSED, TM_LIST>(p, cols, &sm.note[0][live ? k : 0], live ? sm.n_note[k] : 0u, live ? sm.n_tr[k] : 0u, live,
+                                         live && rng[k].z == 0xffffffffu, s, live ? (size_t)sm.sidx[k] : (size_t)0, (uint32_t)(q0 + k), h,
+                                         lane, cut, n_match, n_low, n_unlisted, [A](uint32_t o) { return A + o; },
+                                         [A](uint32_t g) { return g - A; }, big_list, big_count, w);
       }
       __syncthreads();   // every thread is done with the tile before the next bulk copy overwrites it
       i0 = i1;
     }
     __syncthreads();     // the span staging and the hash are reused by the next chunk
   }
-  // counters: lanes -> warp -> block -> one atomic
-  for (int o = 16; o; o >>= 1) {
-    w_matched += __shfl_xor_sync(0xffffffffu, w_matched, o);
-    w_low += __shfl_xor_sync(0xffffffffu, w_low, o);
-    w_drop += __shfl_xor_sync(0xffffffffu, w_drop, o);
-    w_cand += __shfl_xor_sync(0xffffffffu, w_cand, o);
-    w_kept += __shfl_xor_sync(0xffffffffu, w_kept, o);
-  }
-  if (lane == 0) {
-    if (w_matched) atomicAdd(&sm.cnt[0], w_matched);
-    if (w_low) atomicAdd(&sm.cnt[1], w_low);
-    if (w_drop) atomicAdd(&sm.cnt[2], w_drop);
-    if (w_cand) atomicAdd(&sm.cnt[3], w_cand);
-    if (w_kept) atomicAdd(&sm.cnt[4], w_kept);
-  }
-  __syncthreads();
-  if (tid < 5 && sm.cnt[tid]) atomicAdd(&p.counters[tid], sm.cnt[tid]);
+  flush_totals(w, sm.cnt, p.counters);
 }
 
 #include "join_ring.cuh"

@@ -11,10 +11,10 @@
 // the next tile starts where this one ended and only gathers the positions behind what is already resident.  Events
 // that stay are probed again against the new tile's trace-id hash from shared memory (no global access).
 //
-// Everything else — hash probe for tier 1 (dns.go:58-60), two threads per span for tiers 2-4 (dns.go:61-73), counted
-// tier 4 in tiles of one (service, node) class, notes ordered in registers (correlator.go:92-104), the write of the
-// candidates, attributes, confidence and counters (correlator.go:101-118) — is k_join_tiles' code with `position - A`
-// replaced by `position mod RG_CAP`.
+// Everything else is shared with k_join_tiles: the hash probe for tier 1 (dns.go:58-60) has the same shape, tiers 2-4
+// (dns.go:61-73, two threads per span, counted tier 4 in tiles of one (service, node) class) go through pair_scan, and
+// the ordering of the notes and the write of the candidates, attributes, confidence and counters
+// (correlator.go:92-118) through span_epilogue, with `position mod RG_CAP` where the fixed tile uses `position - A`.
 #pragma once
 
 constexpr int RG_CAP = 2048;                 // events resident per CTA (28 B each)
@@ -54,9 +54,8 @@ k_join_ring(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_lis
   extern __shared__ __align__(128) unsigned char smem_raw[];
   RingSmem &sm = *reinterpret_cast<RingSmem *>(smem_raw);
   const unsigned tid = threadIdx.x, lane = tid & 31;
-  const double nan = __longlong_as_double(0x7ff8000000000000ll);
   if (tid < 5) sm.cnt[tid] = 0;
-  unsigned long long w_matched = 0, w_low = 0, w_drop = 0, w_cand = 0, w_kept = 0;
+  TileTotals w;
   const uint64_t W = (uint64_t)p.window_ns;
   const uint64_t Wi = W < (uint64_t)(500 * kMs) ? W : (uint64_t)(500 * kMs);
   // confidence falls with the tier (1.0, 0.9, 0.8, 0.65), so "confidence >= threshold" is "tier <= cut"
@@ -263,107 +262,14 @@ k_join_ring(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_lis
         }
       }
       __syncwarp();      // the two lanes of a span sit in one warp: their notes are visible to each other now
-      // ---- order: lane h takes the notes of parity h, then the odd lane hands its best F to the even lane
-      TopF<F> top;
-      top.init();
-      uint32_t n_cand = 0;
-      bool redo = false;
-      if (live) {
-        n_cand = sm.n_note[k];
-        redo = n_cand > (uint32_t)RG_LIST || sm.rng[k].z == 0xffffffffu;
-        if (!redo) {
-#pragma unroll 2
-          for (uint32_t i = h; i < n_cand; i += 2) {
-            const uint32_t e = sm.note[i][k];
-            const uint32_t sl = e & 0xfffu, tier = e >> 12;
-            const uint32_t g = A + ((sl - A) & RG_MASK);   // the resident position that lives in that slot
-            const uint64_t adt = lsg_absdiff(s.ts, sm.ts[sl]);
-            top.insert(((uint64_t)tier << 56) | adt, p.ev_perm[g], g);
-          }
-        }
-      }
-#pragma unroll
-      for (int r = 0; r < F; ++r) {
-        const uint64_t ok = __shfl_down_sync(0xffffffffu, top.k1[r], 1);
-        const uint32_t oi = __shfl_down_sync(0xffffffffu, top.idx[r], 1);
-        const uint32_t op = __shfl_down_sync(0xffffffffu, top.pos[r], 1);
-        if (!h && oi != 0xffffffffu) top.insert(ok, oi, op);
-      }
-      n_match += __shfl_down_sync(0xffffffffu, n_match, 1);
-      n_low += __shfl_down_sync(0xffffffffu, n_low, 1);
-      n_unlisted += __shfl_down_sync(0xffffffffu, n_unlisted, 1);
-      n_cand += n_unlisted;   // candidates that were counted without being noted
-      // ---- write: the even lane owns the span's candidates, confidence and counters; the twelve attribute columns
-      //      are split between the two lanes (six each), which both read the kept candidates' values and signals
-      if (live) {
-        if (redo) {
-          if (!h) big_list[atomicAdd(big_count, 1u)] = (uint32_t)(q + k);   // more candidates than the list holds
-        } else {
-          const unsigned pair = 3u << (lane & 30u);
-          const size_t si = sm.sidx[k];
-          double vals[F];
-          unsigned sigs[F];
-          unsigned present = 0;
-          int kept = 0;
-#pragma unroll
-          for (int r = 0; r < F; ++r) {
-            const bool mine = r < p.fanout && top.idx[r] != 0xffffffffu;
-            const uint32_t pos = __shfl_sync(pair, mine ? top.pos[r] : 0xffffffffu, lane & 30u);   // the even lane's final list
-            const bool has = pos != 0xffffffffu;
-            const uint32_t in_idx = __shfl_sync(pair, top.idx[r], lane & 30u);
-            vals[r] = has ? p.events_in[in_idx].value : 0.0;
-            sigs[r] = has ? (sm.trsig[pos & RG_MASK] & 15u) : 0xffu;
-            kept += has;
-            present |= sigs[r] < LSG_NSIG ? 1u << sigs[r] : 0u;
-            if (!h && r < p.fanout) {
-              p.cand_event[si * (size_t)p.fanout + r] = has ? top.idx[r] : LSG_NONE;      // correlator.go:101-104
-              p.cand_tier[si * (size_t)p.fanout + r] = has ? (uint8_t)(top.k1[r] >> 56) : (uint8_t)0;
-              if (p.cand_value) p.cand_value[si * (size_t)p.fanout + r] = vals[r];
-              if (p.cand_sig) p.cand_sig[si * (size_t)p.fanout + r] = (uint8_t)sigs[r];
-            }
-          }
-          // per-attribute max over the kept candidates (correlator.go:106-112), one attribute at a time from registers
-          double v0 = nan, v3 = nan, v4 = nan;
-          const bool to_incident = p.inc_keys && s.incident != LSG_NONE && s.incident < p.n_incidents;
-#pragma unroll
-          for (int c = 0; c < LSG_NSIG / 2; ++c) {
-            const unsigned col = h * (LSG_NSIG / 2) + c;
-            double v = p.attr_base ? p.attr_base[si * LSG_NSIG + col] : nan;
-            if ((present >> col) & 1u) {
-#pragma unroll
-              for (int r = 0; r < F; ++r)
-                if (sigs[r] == col && (isnan(v) || vals[r] > v)) v = vals[r];
-            }
-            if (p.attr_out) p.attr_out[si * LSG_NSIG + col] = v;
-            if (to_incident && !isnan(v)) {
-              atomicMax(&p.inc_keys[(size_t)s.incident * LSG_NSIG + col], f64_key(v));   // A7 glue: max per incident and signal
-              if (p.feat) feat_add(p.feat, (size_t)s.incident * LSG_NSIG + col, v);
-            }
-            if (c == 0) v0 = v;   // on the even lane: dns (0), connect (3), tls (4)
-            if (c == 3) v3 = v;
-            if (c == 4) v4 = v;
-          }
-          if (!h) {
-            const uint32_t n_tr = sm.n_tr[k];
-            n_match += n_tr;
-            if (cut < 1) n_low += n_tr;
-            // llm.ebpf.correlation_confidence = the first kept candidate's confidence (correlator.go:113-118)
-            if (p.conf_out) p.conf_out[si] = kept ? lsg_tier_conf((int)(top.k1[0] >> 56)) : 0.0;
-            if (p.retrieval_out) {   // DecomposeRetrieval, correlator.go:179-194: dns + connect + tls in that order
-              double total = 0.0;
-              if (!isnan(v0)) total += v0;
-              if (!isnan(v3)) total += v3;
-              if (!isnan(v4)) total += v4;
-              p.retrieval_out[si] = total;
-            }
-            if (p.n_cand_out) p.n_cand_out[si] = n_cand;
-            w_matched += n_match;
-            w_low += n_low;
-            w_cand += n_cand;
-            w_kept += kept;
-            if (n_cand > (uint32_t)p.fanout) w_drop += n_cand - p.fanout;   // correlator.go:101-103
-          }
-        }
+      // ---- order the span's notes, write its outputs (span_epilogue, join.cu)
+      {
+        const TileCols cols{sm.ts, sm.pod, sm.cls, sm.pid, sm.conn, sm.trsig};
+        span_epilogue<F, true, RG_LIST>(p, cols, &sm.note[0][live ? k : 0], live ? sm.n_note[k] : 0u, live ? sm.n_tr[k] : 0u, live,
+                                        live && sm.rng[k].z == 0xffffffffu, s, live ? (size_t)sm.sidx[k] : (size_t)0, (uint32_t)(q + k), h,
+                                        lane, cut, n_match, n_low, n_unlisted,
+                                        [A](uint32_t sl) { return A + ((sl - A) & RG_MASK); },   // the resident position in that slot
+                                        [](uint32_t g) { return g & RG_MASK; }, big_list, big_count, w);
       }
       __syncthreads();   // every thread is done with the staged spans and with the slots the next tile overwrites
       q += n_fit;
@@ -371,21 +277,5 @@ k_join_ring(const __grid_constant__ JoinParams p, uint32_t *__restrict__ big_lis
       have = true;
     }
   }
-  // counters: lanes -> warp -> block -> one atomic
-  for (int o = 16; o; o >>= 1) {
-    w_matched += __shfl_xor_sync(0xffffffffu, w_matched, o);
-    w_low += __shfl_xor_sync(0xffffffffu, w_low, o);
-    w_drop += __shfl_xor_sync(0xffffffffu, w_drop, o);
-    w_cand += __shfl_xor_sync(0xffffffffu, w_cand, o);
-    w_kept += __shfl_xor_sync(0xffffffffu, w_kept, o);
-  }
-  if (lane == 0) {
-    if (w_matched) atomicAdd(&sm.cnt[0], w_matched);
-    if (w_low) atomicAdd(&sm.cnt[1], w_low);
-    if (w_drop) atomicAdd(&sm.cnt[2], w_drop);
-    if (w_cand) atomicAdd(&sm.cnt[3], w_cand);
-    if (w_kept) atomicAdd(&sm.cnt[4], w_kept);
-  }
-  __syncthreads();
-  if (tid < 5 && sm.cnt[tid]) atomicAdd(&p.counters[tid], sm.cnt[tid]);
+  flush_totals(w, sm.cnt, p.counters);
 }
