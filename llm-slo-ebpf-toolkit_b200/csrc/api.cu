@@ -356,7 +356,15 @@ int lsg_last_sort_info(const lsg_ctx *ctx, uint32_t *key_bits, uint32_t *time_sh
   if (!ctx) return LSG_ERR_INVALID;
   if (key_bits) *key_bits = ctx->last_key.bits;
   if (time_shift) *time_shift = ctx->last_key.shift;
-  if (passes) *passes = (ctx->last_key.bits + 7) / 8;
+  if (passes) {
+    // as radix_sort_pairs shares the key's bits: as few passes as 10-bit digits allow, digits of equal width, never
+    // narrower than 8 bits (what the radix path runs; the counting sort of small key spaces has no passes)
+    const uint32_t bits = ctx->last_key.bits ? ctx->last_key.bits : 1;
+    const uint32_t most = (bits + 9) / 10;
+    uint32_t width = (bits + most - 1) / most;
+    if (width < 8) width = 8;
+    *passes = (bits + width - 1) / width;
+  }
   return 0;
 }
 

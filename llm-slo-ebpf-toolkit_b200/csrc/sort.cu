@@ -18,10 +18,11 @@
 //   counting sort  (key space <= 2^25, not exact)  one counter per key in an L2-resident table:
 //                  k_count_keys (key + rank by returning atomic) -> exclusive scan -> k_place_events
 //                  (permutation).  Order inside one key = whatever the atomics gave.
-//   LSD radix sort (larger key spaces, spans, the exact entry point)  stable; per pass: per-tile digit
-//                  histogram -> per-digit scan over tiles -> scatter of (key, index) pairs.  Ranking inside
-//                  a tile is warp-synchronous (peer masks from eight ballots, one shared-memory counter
-//                  row per warp, no atomics); items are staged in shared memory in digit order so that the
+//   LSD radix sort (larger key spaces, spans, the exact entry point)  stable; digits of 8-10 bits that share the
+//                  key's bits evenly (29 bits: three passes); per pass: per-tile digit histogram (shared-memory
+//                  atomics) -> per-digit scan over tiles -> scatter of (key, index) pairs.  Ranking inside
+//                  a tile is warp-synchronous (peer masks from one ballot per digit bit, one 16-bit shared-memory
+//                  counter row per warp, no atomics); items are staged in shared memory in digit order so that the
 //                  global writes are coalesced runs.  No inter-CTA spin-waits: tiles only communicate
 //                  through the scanned histogram.
 #include "common.cuh"
